@@ -1,0 +1,152 @@
+/*
+ * me_b200.h -- C ABI of the B200-native displacement-search library (libme_b200.so).
+ *
+ * This is the drop-in boundary for the hot path of ruzko/motion-estimation: the per-frame-pair
+ * displacement estimate and its reduction to one (pdx, pdy, flag) per pair.  The reference has no
+ * FFI or plugin interface (it is three Python scripts); the entry points below are what a ctypes
+ * binding for its two call sites needs:
+ *
+ *     calc_ECC_transform(prevFrame, curFrame) -> (pdx, pdy, measurement_flag)
+ *         estimate_vel_vid.py:306-369 (caller :522) and estimate_vel.py:286-297 (caller :361)
+ *     end_process(clean_arrs) pair loop
+ *         estimate_vel_vid.py:493-583, estimate_vel.py:333-378
+ *
+ * Conventions: plain C types only, no exceptions, every function returns 0 (ME_OK) or a negative
+ * ME_E* code and leaves a message for me_last_error().  The caller owns every host buffer it
+ * passes; the library owns all device memory.  One context per GPU; a context is thread-compatible
+ * (use it from one thread at a time), contexts on different GPUs are independent.
+ *
+ * Displacements are in FULL-resolution pixels, +x content motion gives pdx > 0 (the reference's
+ * sign).  The Python wrapper halves them where it emulates the video script, whose ECC result is in
+ * half-resolution pixels (estimate_vel_vid.py:330,342-346,358).
+ *
+ * The search itself is specified in oracle/sad_oracle.c ("the spec"): full-search SAD over BxB
+ * blocks and +-R displacements restricted to in-frame candidates, first-minimum-in-raster-order
+ * tie-break, per-axis 3-point parabola refinement, per-axis median over textured+peaked blocks.
+ */
+#ifndef ME_B200_H
+#define ME_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ME_OK            0
+#define ME_EINVAL       -1   /* bad argument (sizes, NULL, slot out of range ...)            */
+#define ME_EUNSUPPORTED -2   /* legal in the spec but not built yet (see message)             */
+#define ME_ECUDA        -3   /* a CUDA runtime/driver call failed; message has the CUDA text  */
+#define ME_ENOMEM       -4
+#define ME_ESTATE       -5   /* call order (fetch before search ...)                          */
+
+/* per-block flag bits (same values as oracle/sad_oracle.c) */
+#define ME_FLAG_TEXTURED   1u
+#define ME_FLAG_X_INTERIOR 2u
+#define ME_FLAG_Y_INTERIOR 4u
+#define ME_FLAG_X_PEAKED   8u
+#define ME_FLAG_Y_PEAKED   16u
+
+typedef struct me_ctx me_ctx;
+
+/* Search parameters.  The reference has none of these (its ECC call takes motionType/criteria,
+ * estimate_vel_vid.py:308-309); they are the knobs of the block search that replaces it. */
+typedef struct me_params {
+    int32_t block;      /* B: 8, 16 or 32                                                     */
+    int32_t range;      /* R: 1 .. (256 - B) / 2   (one TMA box per window; larger R: later)  */
+    int32_t min_range;  /* texture gate: block max-min >= min_range grey levels               */
+    int32_t subpixel;   /* 0 = integer displacements only                                     */
+    int32_t min_valid;  /* pair flag = nvalid_x >= max(min_valid, 1)                          */
+    int32_t min_curv;   /* peak gate on cm - 2 c0 + cp; values < 1 mean 1                     */
+} me_params;
+
+/* One record per frame pair: replaces the (pdx, pdy, measurement_flag) tuple returned at
+ * estimate_vel_vid.py:369. */
+typedef struct me_pair_result {
+    float   pdx, pdy;       /* full-resolution pixels                                         */
+    int32_t flag;           /* 1 = measurement accepted (the reference's measurement_flag)    */
+    int32_t nvalid_x;       /* blocks that entered the x median                               */
+    int32_t nvalid_y;
+    int32_t reserved;
+} me_pair_result;
+
+/* Static information about a context's geometry. */
+typedef struct me_geometry {
+    int32_t height, width;
+    int32_t nbx, nby;           /* block grid (floor)                                         */
+    int32_t max_frames;         /* ring slots                                                 */
+    int32_t max_pairs;          /* pairs per me_search call                                   */
+    int32_t tile_blocks_x;      /* blocks per CTA tile                                        */
+    int32_t threads_per_cta;
+    int32_t smem_bytes;
+    int32_t tiles_per_pair;     /* == CTAs per pair                                           */
+    int64_t cand_px_per_pair;         /* blocks * B^2 * (2R+1)^2 (nominal, what the ALU executes) */
+    int64_t cand_px_per_pair_valid;   /* in-frame candidates only (algorithmic work)              */
+    int32_t sm_count;
+    int32_t uses_tma;
+} me_geometry;
+
+const char *me_last_error(void);          /* thread-local, never NULL                         */
+const char *me_version(void);
+
+/* Create a context on CUDA device `device` for frames of height x width luma bytes.
+ * Allocates the device frame ring (max_frames slots), pinned staging and result buffers. */
+int me_create(int device, int height, int width, const me_params *params, int max_frames, int max_pairs,
+              me_ctx **out);
+int me_destroy(me_ctx *ctx);
+int me_get_geometry(const me_ctx *ctx, me_geometry *out);
+
+/* Frame ingest -- replaces the decode-and-stack loop at estimate_vel_vid.py:165-195 from the point
+ * where luma bytes exist.  Copies n_frames frames (row_pitch bytes between rows, frames contiguous:
+ * frame f starts at luma + f*height*row_pitch) into the pinned staging ring and from there to device
+ * slots first_slot.. with cudaMemcpyAsync on the copy stream.  Returns once the host buffer may be
+ * reused; the device copy may still be in flight (me_search orders itself after it). */
+int me_upload(me_ctx *ctx, const uint8_t *luma, size_t row_pitch, int first_slot, int n_frames);
+
+/* Same for interleaved BGR frames as cv.VideoCapture delivers them (estimate_vel_vid.py:173-178):
+ * the BGR2GRAY conversion runs on the GPU, bit-exact with cv.cvtColor's 14-bit fixed point. */
+int me_upload_bgr(me_ctx *ctx, const uint8_t *bgr, size_t row_pitch, int first_slot, int n_frames);
+
+/* Launch the search for n_pairs pairs of ring slots: pairs[2k] = previous frame, pairs[2k+1] =
+ * current frame.  Asynchronous; results are read with me_fetch_*.  This is the call that replaces
+ * the body of calc_ECC_transform for a whole batch. */
+int me_search(me_ctx *ctx, const int32_t *pairs, int n_pairs);
+
+/* Wait for the last me_search and copy its per-pair records to `out` (n_pairs of them). */
+int me_fetch_pairs(me_ctx *ctx, me_pair_result *out, int n_pairs);
+
+/* Per-block results of pair `pair_index` of the last me_search; any pointer may be NULL.
+ * Layouts (row-major over by, bx): mv int16[nb][2] (dx,dy); sad uint32[nb]; sub float[nb][2];
+ * flags uint8[nb].  This is the dense field the reference only has through Farneback
+ * (estimate_vel_vid.py:385-391). */
+int me_fetch_blocks(me_ctx *ctx, int pair_index, int16_t *mv, uint32_t *sad, float *sub, uint8_t *flags);
+
+/* One-shot: upload two host frames, search, fetch.  What calc_ECC_transform(prev, cur) binds. */
+int me_estimate_pair(me_ctx *ctx, const uint8_t *prev, const uint8_t *cur, size_t row_pitch,
+                     me_pair_result *out);
+
+/* Search frames that already live in device memory (e.g. a torch uint8 tensor): d_frames is
+ * (n_frames, height, pitch) with pitch % 16 == 0 and a 16-byte aligned base.  Uses the context's
+ * result buffers; `stream` is a cudaStream_t (NULL = the context's compute stream). */
+int me_search_device(me_ctx *ctx, const uint8_t *d_frames, size_t pitch, int n_frames, const int32_t *pairs,
+                     int n_pairs, void *stream);
+
+int me_sync(me_ctx *ctx);
+
+/* Device time of the most recent search kernel, measured with CUDA events on its stream. */
+int me_last_search_ms(me_ctx *ctx, float *ms);
+/* Number of kernels this context has launched so far (search, ingest conversion ...). */
+int64_t me_launch_count(const me_ctx *ctx);
+
+/* Integer-SAD issue-rate microbenchmark: runs a register-only VABSDIFF4 loop on every SM and
+ * reports VABSDIFF4 thread-instructions per clock per SM and the SM clock it saw.  Used by bench.py
+ * to put a measured number under the integer-ALU roofline.  mode 0 = SAD ops only; 1 = one extra
+ * ALU-pipe op per SAD op; 2 = one extra FMA-pipe op (IMAD) per SAD op; 3 = one LDS.128 per 16. */
+int me_microbench_vabsdiff4(int device, int mode, double *instr_per_clk_per_sm, double *sm_mhz_seen,
+                            int *sm_count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ME_B200_H */

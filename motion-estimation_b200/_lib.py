@@ -1,0 +1,118 @@
+"""ctypes binding of libme_b200.so -- the C ABI declared in include/me_b200.h.
+
+There is no CPU fallback here by design: if the CUDA library has not been built, or cannot be
+loaded, importing the binding raises with the build command to run.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import shutil
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_CSRC = os.path.join(_HERE, "csrc")
+SO_PATH = os.path.join(_HERE, "libme_b200.so")
+HEADER = os.path.normpath(os.path.join(_HERE, "..", "include", "me_b200.h"))
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+              "-shared", "-Xcompiler", "-fPIC"]
+
+
+class MEError(RuntimeError):
+    """A libme_b200 call returned a negative status."""
+
+    def __init__(self, code, msg):
+        super().__init__(f"libme_b200 error {code}: {msg}")
+        self.code = code
+
+
+class Params(C.Structure):
+    _fields_ = [("block", C.c_int32), ("range", C.c_int32), ("min_range", C.c_int32),
+                ("subpixel", C.c_int32), ("min_valid", C.c_int32), ("min_curv", C.c_int32)]
+
+
+class PairResult(C.Structure):
+    _fields_ = [("pdx", C.c_float), ("pdy", C.c_float), ("flag", C.c_int32),
+                ("nvalid_x", C.c_int32), ("nvalid_y", C.c_int32), ("reserved", C.c_int32)]
+
+
+class Geometry(C.Structure):
+    _fields_ = [("height", C.c_int32), ("width", C.c_int32), ("nbx", C.c_int32), ("nby", C.c_int32),
+                ("max_frames", C.c_int32), ("max_pairs", C.c_int32), ("tile_blocks_x", C.c_int32),
+                ("threads_per_cta", C.c_int32), ("smem_bytes", C.c_int32), ("tiles_per_pair", C.c_int32),
+                ("cand_px_per_pair", C.c_int64), ("cand_px_per_pair_valid", C.c_int64),
+                ("sm_count", C.c_int32), ("uses_tma", C.c_int32)]
+
+
+def sources():
+    return [os.path.join(_CSRC, "me_api.cu"), os.path.join(_CSRC, "sad_search.cuh"), HEADER]
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile csrc/ for sm_100a with nvcc into libme_b200.so next to this file (in-tree)."""
+    srcs = sources()
+    if not force and os.path.exists(SO_PATH) and all(os.path.getmtime(SO_PATH) >= os.path.getmtime(s) for s in srcs):
+        return SO_PATH
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO_PATH, srcs[0]]
+    env = dict(os.environ)
+    env.pop("CC", None)
+    env.pop("CXX", None)
+    subprocess.run(cmd, check=True, env=env)
+    return SO_PATH
+
+
+_lib = None
+
+
+def lib():
+    """The loaded library with argtypes set.  Raises (never falls back) when it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(SO_PATH):
+        raise ImportError(
+            f"{SO_PATH} is missing: the CUDA extension has not been built. Run "
+            "`python -c 'import __graft_entry__ as g; g.build()'` (needs nvcc; no GPU needed to compile). "
+            "There is deliberately no CPU fallback for the displacement search.")
+    L = C.CDLL(SO_PATH)
+    vp, i32p, u8p = C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_uint8)
+    L.me_last_error.restype = C.c_char_p
+    L.me_version.restype = C.c_char_p
+    L.me_create.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(Params), C.c_int, C.c_int, C.POINTER(vp)]
+    L.me_destroy.argtypes = [vp]
+    L.me_get_geometry.argtypes = [vp, C.POINTER(Geometry)]
+    L.me_upload.argtypes = [vp, vp, C.c_size_t, C.c_int, C.c_int]
+    L.me_upload_bgr.argtypes = [vp, vp, C.c_size_t, C.c_int, C.c_int]
+    L.me_search.argtypes = [vp, i32p, C.c_int]
+    L.me_fetch_pairs.argtypes = [vp, C.POINTER(PairResult), C.c_int]
+    L.me_fetch_blocks.argtypes = [vp, C.c_int, vp, vp, vp, vp]
+    L.me_estimate_pair.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(PairResult)]
+    L.me_search_device.argtypes = [vp, vp, C.c_size_t, C.c_int, i32p, C.c_int, vp]
+    L.me_sync.argtypes = [vp]
+    L.me_last_search_ms.argtypes = [vp, C.POINTER(C.c_float)]
+    L.me_launch_count.argtypes = [vp]
+    L.me_launch_count.restype = C.c_int64
+    L.me_microbench_vabsdiff4.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                          C.POINTER(C.c_int)]
+    for name in ("me_create", "me_destroy", "me_get_geometry", "me_upload", "me_upload_bgr", "me_search",
+                 "me_fetch_pairs", "me_fetch_blocks", "me_estimate_pair", "me_search_device", "me_sync",
+                 "me_last_search_ms", "me_microbench_vabsdiff4"):
+        getattr(L, name).restype = C.c_int
+    _lib = L
+    return L
+
+
+def check(rc):
+    if rc < 0:
+        raise MEError(rc, lib().me_last_error().decode("utf-8", "replace"))
+    return rc
+
+
+def exported_symbols():
+    """Names declared in include/me_b200.h (parsed from the header, used by the ABI test)."""
+    import re
+    text = open(HEADER).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(me_[a-z0-9_]+)\s*\(", text)))

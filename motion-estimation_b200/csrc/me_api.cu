@@ -1,0 +1,595 @@
+// me_api.cu -- host side of libme_b200.so: the C ABI declared in include/me_b200.h.
+//
+// Owns the device frame ring, the pinned staging buffers, the two streams (copy / compute), the TMA
+// descriptors and the launch configuration.  There is no CPU fallback: every entry point either
+// runs the CUDA path or returns an error.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <string>
+#include <vector>
+
+#include "../../include/me_b200.h"
+#include "sad_search.cuh"
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CU_TRY(expr)                                                                              \
+    do {                                                                                          \
+        cudaError_t e_ = (expr);                                                                  \
+        if (e_ != cudaSuccess)                                                                    \
+            return fail(ME_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+inline int round_up(int a, int b) { return ceil_div(a, b) * b; }
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled_fn()
+{
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// (x, y, frame) uint8 view of a frame stack; a box is box_w x box_h bytes of one frame.
+int make_tensor_map(CUtensorMap *tm, const uint8_t *base, int W, int H, int n_frames, size_t pitch,
+                    int box_w, int box_h)
+{
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) return fail(ME_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    cuuint64_t dims[3] = {(cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)n_frames};
+    cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)pitch * (cuuint64_t)H};
+    cuuint32_t box[3] = {(cuuint32_t)box_w, (cuuint32_t)box_h, 1u};
+    cuuint32_t estr[3] = {1u, 1u, 1u};
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<uint8_t *>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail(ME_ECUDA, "cuTensorMapEncodeTiled failed (CUresult %d; W=%d H=%d pitch=%zu box=%dx%d)", (int)r, W,
+                    H, pitch, box_w, box_h);
+    return ME_OK;
+}
+
+struct KernelChoice {
+    const void *fn;
+    int ndy, nq, maxt;
+};
+
+template <int B, int NDY, int NQ, bool K64, int MAXT, int MINB>
+KernelChoice choice()
+{
+    return KernelChoice{(const void *)&me::sad_search_kernel<B, NDY, NQ, K64, MAXT, MINB>, NDY, NQ, MAXT};
+}
+
+// The patch shapes per block size (see DESIGN.md "inner loop").
+KernelChoice pick_kernel(int B, bool k64)
+{
+    switch (B) {
+    case 8:  return k64 ? choice<8, 5, 8, true, 512, 1>() : choice<8, 5, 8, false, 512, 1>();
+    case 16: return k64 ? choice<16, 5, 4, true, 512, 1>() : choice<16, 5, 4, false, 512, 1>();
+    default: return k64 ? choice<32, 4, 4, true, 512, 1>() : choice<32, 4, 4, false, 512, 1>();
+    }
+}
+
+int env_int(const char *name, int dflt)
+{
+    const char *v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+
+} // namespace
+
+struct me_ctx {
+    int device = 0;
+    int H = 0, W = 0;
+    me_params p{};
+    int max_frames = 0, max_pairs = 0;
+    size_t pitch = 0, frame_stride = 0;
+    uint8_t *d_frames = nullptr;
+    // staging
+    uint8_t *h_stage[2] = {nullptr, nullptr};
+    size_t stage_bytes = 0;
+    cudaEvent_t stage_free[2] = {nullptr, nullptr};
+    int stage_next = 0;
+    uint8_t *d_bgr = nullptr;
+    size_t d_bgr_bytes = 0;
+    // streams / events
+    cudaStream_t s_copy = nullptr, s_compute = nullptr;
+    cudaEvent_t ev_upload = nullptr, ev_search = nullptr, ev_k0 = nullptr, ev_k1 = nullptr;
+    bool have_upload = false, have_search = false;
+    // pairs + results
+    int32_t *h_pairs = nullptr, *d_pairs = nullptr;
+    me_pair_result *h_pair_out = nullptr;
+    int last_pairs = 0;
+    // launch configuration
+    me::SearchArgs args{};
+    CUtensorMap tm_win{}, tm_ref{};
+    KernelChoice kc{};
+    int threads = 0, smem = 0, sm_count = 0;
+    int64_t launches = 0;
+    int64_t cand_px = 0, cand_px_valid = 0;
+};
+
+namespace {
+
+// Fill ctx->args / launch shape for the context's geometry.  Returns ME_OK or an error.
+int configure(me_ctx *c)
+{
+    const int B = c->p.block, R = c->p.range, U = 2 * R + 1, W = c->W, H = c->H;
+    me::SearchArgs &a = c->args;
+    a.W = W; a.H = H; a.R = R; a.U = U;
+    a.nbx = W / B; a.nby = H / B; a.nb = a.nbx * a.nby;
+    a.frame_pitch = (int)c->pitch;
+    a.frame_stride = (long long)c->frame_stride;
+    a.min_range = c->p.min_range; a.min_curv = c->p.min_curv; a.subpixel = c->p.subpixel; a.min_valid = c->p.min_valid;
+
+    int rb = 0;
+    while ((1ll << rb) < (long long)U * U) ++rb;
+    a.rank_bits = rb;
+    const long long sad_max = (long long)B * B * 255;
+    const bool k64 = ((sad_max + 1) << rb) > (1ll << 32);
+    c->kc = pick_kernel(B, k64);
+    const int NDY = c->kc.ndy, NQ = c->kc.nq;
+
+    a.ndyg = ceil_div(U, NDY);
+    a.cg_start[0] = 0;
+    for (int s = 0; s < 4; ++s) {
+        const int nq = (2 * R - s) >= 0 ? (2 * R - s) / 4 + 1 : 0;
+        a.cg_start[s + 1] = a.cg_start[s] + ceil_div(nq, NQ);
+    }
+    a.per_j = a.ndyg * a.cg_start[4];
+
+    // Rows: every dy group reads B + NDY - 1 window rows starting at dyg*NDY.
+    const int win_rows = a.ndyg * NDY + B - 1;
+    a.n_row_boxes = ceil_div(win_rows, 256);
+    a.box_rows = ceil_div(win_rows, a.n_row_boxes);
+    const int alloc_rows = a.n_row_boxes * a.box_rows;
+
+    // Tile width: the widest tile whose window still fits one TMA box (<= 256 B) and leaves room for
+    // >= 2 CTAs per SM; narrower when the frame is too small to fill the GPU otherwise.
+    const int smem_cap = env_int("ME_SMEM_CAP", 100 * 1024);
+    int best_tbx = 0;
+    const int forced = env_int("ME_TBX", 0);
+    for (int tbx = me::kMaxTbx; tbx >= 1; --tbx) {
+        if ((tbx * B) % 16) continue;
+        if (forced && tbx != forced) continue;
+        const int need = tbx * B + 2 * R;
+        int pitch = round_up(need, 16);
+        if ((NDY & 1) && ((pitch / 16) & 1) == 0 && pitch + 16 <= 256) pitch += 16;   // odd 16-B pitch: conflict-free dy groups
+        if (pitch > 256) continue;
+        const int copy = round_up(alloc_rows * pitch, 128);
+        const int smem = 4 * copy + 256 + round_up(tbx * B * B, 128) + me::kMaxTbx * 8 + 64;
+        if (smem > 227 * 1024) continue;
+        const long long tiles = (long long)ceil_div(a.nbx, tbx) * a.nby;
+        if (!forced) {
+            if (smem > smem_cap && tbx > 1) continue;
+            if (tbx > 1 && tiles * (c->max_pairs > 4 ? 4 : c->max_pairs) < 2ll * c->sm_count && tbx * B > 16) continue;
+        }
+        best_tbx = tbx;
+        a.tbx = tbx; a.win_pitch = pitch; a.copy_bytes = copy; a.ref_pitch = tbx * B;
+        c->smem = smem;
+        break;
+    }
+    if (!best_tbx)
+        return fail(ME_EUNSUPPORTED, "block %d with range %d needs a %d-byte window row; one TMA box holds 256 "
+                    "(range <= %d for this block size)", B, R, B + 2 * R, (256 - B) / 2);
+    a.tiles_x = ceil_div(a.nbx, a.tbx);
+    a.tiles_per_pair = a.tiles_x * a.nby;
+
+    // Threads: a multiple of 32 that wastes the fewest lanes on a full tile.
+    const int total = a.tbx * a.per_j;
+    int best_t = 128;
+    double best_eff = -1;
+    const int tmax = env_int("ME_THREADS_MAX", 256);
+    for (int t = 128; t <= tmax && t <= c->kc.maxt; t += 32) {
+        const double eff = (double)total / ((double)ceil_div(total, t) * t);
+        if (eff >= best_eff - 1e-9) { best_eff = eff; best_t = t; }
+    }
+    c->threads = env_int("ME_THREADS", best_t);
+    if (c->threads % 32 || c->threads < 32 || c->threads > c->kc.maxt)
+        return fail(ME_EINVAL, "ME_THREADS=%d is not a multiple of 32 in [32,%d]", c->threads, c->kc.maxt);
+    a.use_tma = env_int("ME_NO_TMA", 0) ? 0 : 1;
+
+    // Work accounting: nominal = what the ALU executes, valid = in-frame candidates.
+    c->cand_px = (long long)a.nb * B * B * U * U;
+    long long valid = 0;
+    for (int by = 0; by < a.nby; ++by) {
+        const int y0 = by * B;
+        const int ny = (R < H - B - y0 ? R : H - B - y0) - (-R > -y0 ? -R : -y0) + 1;
+        long long sx = 0;
+        for (int bx = 0; bx < a.nbx; ++bx) {
+            const int x0 = bx * B;
+            sx += (R < W - B - x0 ? R : W - B - x0) - (-R > -x0 ? -R : -x0) + 1;
+        }
+        valid += sx * ny;
+    }
+    c->cand_px_valid = valid * B * B;
+    return ME_OK;
+}
+
+int launch_search(me_ctx *c, const uint8_t *frames, const CUtensorMap &tm_win, const CUtensorMap &tm_ref,
+                  int n_pairs, cudaStream_t st)
+{
+    me::SearchArgs a = c->args;
+    a.frames = frames;
+    a.pairs = c->d_pairs;
+    void *params[3] = {(void *)&tm_win, (void *)&tm_ref, (void *)&a};
+    CU_TRY(cudaEventRecord(c->ev_k0, st));
+    CU_TRY(cudaLaunchKernel(c->kc.fn, dim3((unsigned)(a.tiles_per_pair * n_pairs)), dim3((unsigned)c->threads), params,
+                            (size_t)c->smem, st));
+    CU_TRY(cudaEventRecord(c->ev_k1, st));
+    c->launches += 1;
+    return ME_OK;
+}
+
+int check_pairs(me_ctx *c, const int32_t *pairs, int n_pairs, int n_frames)
+{
+    if (!pairs || n_pairs < 1 || n_pairs > c->max_pairs)
+        return fail(ME_EINVAL, "n_pairs=%d outside 1..%d (or pairs is NULL)", n_pairs, c->max_pairs);
+    for (int i = 0; i < 2 * n_pairs; ++i)
+        if (pairs[i] < 0 || pairs[i] >= n_frames)
+            return fail(ME_EINVAL, "pair %d references frame %d, outside 0..%d", i / 2, pairs[i], n_frames - 1);
+    return ME_OK;
+}
+
+// Host rows -> pinned staging -> device slots, double-buffered on the copy stream.
+int upload_impl(me_ctx *c, const uint8_t *src, size_t row_pitch, int first_slot, int n_frames, bool bgr)
+{
+    const size_t row_bytes = (size_t)c->W * (bgr ? 3 : 1);
+    if (!src || n_frames < 1 || first_slot < 0 || first_slot + n_frames > c->max_frames)
+        return fail(ME_EINVAL, "upload of %d frames at slot %d does not fit the %d-slot ring (or NULL source)", n_frames,
+                    first_slot, c->max_frames);
+    if (row_pitch < row_bytes) return fail(ME_EINVAL, "row_pitch %zu < %zu bytes per row", row_pitch, row_bytes);
+    CU_TRY(cudaSetDevice(c->device));
+    if (c->have_search) CU_TRY(cudaStreamWaitEvent(c->s_copy, c->ev_search, 0));   // do not overwrite frames in use
+    const size_t frame_bytes = row_bytes * c->H;
+    const int per_chunk = (int)(c->stage_bytes / frame_bytes);
+    if (per_chunk < 1) return fail(ME_ENOMEM, "staging buffer smaller than one frame");
+    for (int f = 0; f < n_frames; f += per_chunk) {
+        const int nf = (n_frames - f < per_chunk) ? n_frames - f : per_chunk;
+        const int sb = c->stage_next;
+        c->stage_next ^= 1;
+        CU_TRY(cudaEventSynchronize(c->stage_free[sb]));
+        const uint8_t *s = src + (size_t)f * c->H * row_pitch;
+        if (row_pitch == row_bytes) {
+            memcpy(c->h_stage[sb], s, frame_bytes * nf);
+        } else {
+            for (size_t r = 0; r < (size_t)nf * c->H; ++r) memcpy(c->h_stage[sb] + r * row_bytes, s + r * row_pitch, row_bytes);
+        }
+        uint8_t *dst = c->d_frames + (size_t)(first_slot + f) * c->frame_stride;
+        if (!bgr) {
+            CU_TRY(cudaMemcpy2DAsync(dst, c->pitch, c->h_stage[sb], row_bytes, row_bytes, (size_t)nf * c->H,
+                                     cudaMemcpyHostToDevice, c->s_copy));
+        } else {
+            const size_t need = frame_bytes * nf;
+            if (c->d_bgr_bytes < need) {
+                if (c->d_bgr) { CU_TRY(cudaStreamSynchronize(c->s_copy)); CU_TRY(cudaFree(c->d_bgr)); }
+                c->d_bgr = nullptr; c->d_bgr_bytes = 0;
+                CU_TRY(cudaMalloc(&c->d_bgr, c->stage_bytes));
+                c->d_bgr_bytes = c->stage_bytes;
+            }
+            CU_TRY(cudaMemcpyAsync(c->d_bgr, c->h_stage[sb], need, cudaMemcpyHostToDevice, c->s_copy));
+            dim3 blk(128), grd((unsigned)ceil_div(ceil_div(c->W, 4), 128), (unsigned)(nf * c->H));
+            me::bgr2gray_kernel<<<grd, blk, 0, c->s_copy>>>(c->d_bgr, row_bytes, dst, c->pitch, c->W, nf * c->H);
+            CU_TRY(cudaGetLastError());
+            c->launches += 1;
+        }
+        CU_TRY(cudaEventRecord(c->stage_free[sb], c->s_copy));
+    }
+    CU_TRY(cudaEventRecord(c->ev_upload, c->s_copy));
+    c->have_upload = true;
+    return ME_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+const char *me_last_error(void) { return g_err; }
+const char *me_version(void) { return "me_b200 0.1 (sm_100a; TMA-staged VABSDIFF4 full search)"; }
+
+int me_create(int device, int height, int width, const me_params *params, int max_frames, int max_pairs, me_ctx **out)
+{
+    if (!out) return fail(ME_EINVAL, "out is NULL");
+    *out = nullptr;
+    if (!params) return fail(ME_EINVAL, "params is NULL");
+    const int B = params->block, R = params->range;
+    if (B != 8 && B != 16 && B != 32) return fail(ME_EUNSUPPORTED, "block size %d: built sizes are 8, 16, 32", B);
+    if (R < 1) return fail(ME_EINVAL, "range %d < 1", R);
+    if (height < B || width < B) return fail(ME_EINVAL, "frame %dx%d smaller than one %d-pixel block", width, height, B);
+    if (max_frames < 2 || max_pairs < 1) return fail(ME_EINVAL, "max_frames >= 2 and max_pairs >= 1 required");
+    int ndev = 0;
+    CU_TRY(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(ME_EINVAL, "device %d of %d", device, ndev);
+    CU_TRY(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail(ME_EUNSUPPORTED, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+
+    me_ctx *c = new me_ctx();
+    c->device = device; c->H = height; c->W = width; c->p = *params;
+    c->max_frames = max_frames; c->max_pairs = max_pairs;
+    c->sm_count = prop.multiProcessorCount;
+    c->pitch = (size_t)round_up(width, 16);
+    c->frame_stride = c->pitch * (size_t)height;
+    int rc = configure(c);
+    if (rc) { delete c; return rc; }
+
+#define CREATE_TRY(expr)                                                                                     \
+    do {                                                                                                     \
+        cudaError_t e_ = (expr);                                                                             \
+        if (e_ != cudaSuccess) {                                                                             \
+            fail(ME_ECUDA, "%s failed: %s", #expr, cudaGetErrorString(e_));                                  \
+            me_destroy(c);                                                                                   \
+            return ME_ECUDA;                                                                                 \
+        }                                                                                                    \
+    } while (0)
+
+    const size_t ring = c->frame_stride * (size_t)max_frames + 256;
+    CREATE_TRY(cudaMalloc(&c->d_frames, ring));
+    CREATE_TRY(cudaMemset(c->d_frames, 0, ring));
+    CREATE_TRY(cudaStreamCreateWithFlags(&c->s_copy, cudaStreamNonBlocking));
+    CREATE_TRY(cudaStreamCreateWithFlags(&c->s_compute, cudaStreamNonBlocking));
+    CREATE_TRY(cudaEventCreateWithFlags(&c->ev_upload, cudaEventDisableTiming));
+    CREATE_TRY(cudaEventCreateWithFlags(&c->ev_search, cudaEventDisableTiming));
+    CREATE_TRY(cudaEventCreate(&c->ev_k0));
+    CREATE_TRY(cudaEventCreate(&c->ev_k1));
+    // staging: two buffers, each >= one BGR frame and about 32 MiB for long uploads
+    size_t want = (size_t)width * height * 3;
+    if (want < (32u << 20)) want = 32u << 20;
+    const size_t cap = (size_t)width * height * 3 * (size_t)max_frames;
+    if (want > cap) want = cap;
+    c->stage_bytes = want;
+    for (int i = 0; i < 2; ++i) {
+        CREATE_TRY(cudaHostAlloc(&c->h_stage[i], c->stage_bytes, cudaHostAllocDefault));
+        CREATE_TRY(cudaEventCreateWithFlags(&c->stage_free[i], cudaEventDisableTiming));
+    }
+    CREATE_TRY(cudaHostAlloc(&c->h_pairs, sizeof(int32_t) * 2 * (size_t)max_pairs, cudaHostAllocDefault));
+    CREATE_TRY(cudaHostAlloc(&c->h_pair_out, sizeof(me_pair_result) * (size_t)max_pairs, cudaHostAllocDefault));
+    CREATE_TRY(cudaMalloc(&c->d_pairs, sizeof(int32_t) * 2 * (size_t)max_pairs));
+    const size_t nb = (size_t)c->args.nb * (size_t)max_pairs;
+    CREATE_TRY(cudaMalloc(&c->args.blk_mv, nb * 2 * sizeof(int16_t)));
+    CREATE_TRY(cudaMalloc(&c->args.blk_sad, nb * sizeof(uint32_t)));
+    CREATE_TRY(cudaMalloc(&c->args.blk_sub, nb * 2 * sizeof(float)));
+    CREATE_TRY(cudaMalloc(&c->args.blk_flags, nb));
+    CREATE_TRY(cudaMalloc(&c->args.pair_out, sizeof(me_pair_result) * (size_t)max_pairs));
+    CREATE_TRY(cudaMalloc(&c->args.pair_ticket, sizeof(unsigned) * (size_t)max_pairs));
+    CREATE_TRY(cudaMemset(c->args.pair_ticket, 0, sizeof(unsigned) * (size_t)max_pairs));
+    CREATE_TRY(cudaFuncSetAttribute(c->kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, c->smem));
+#undef CREATE_TRY
+    rc = make_tensor_map(&c->tm_win, c->d_frames, c->W, c->H, max_frames, c->pitch, c->args.win_pitch, c->args.box_rows);
+    if (!rc) rc = make_tensor_map(&c->tm_ref, c->d_frames, c->W, c->H, max_frames, c->pitch, c->args.ref_pitch, B);
+    if (rc) { me_destroy(c); return rc; }
+    *out = c;
+    return ME_OK;
+}
+
+int me_destroy(me_ctx *c)
+{
+    if (!c) return ME_OK;
+    cudaSetDevice(c->device);
+    if (c->s_copy) cudaStreamSynchronize(c->s_copy);
+    if (c->s_compute) cudaStreamSynchronize(c->s_compute);
+    cudaFree(c->d_frames); cudaFree(c->d_bgr); cudaFree(c->d_pairs);
+    cudaFree(c->args.blk_mv); cudaFree(c->args.blk_sad); cudaFree(c->args.blk_sub); cudaFree(c->args.blk_flags);
+    cudaFree(c->args.pair_out); cudaFree(c->args.pair_ticket);
+    for (int i = 0; i < 2; ++i) {
+        if (c->h_stage[i]) cudaFreeHost(c->h_stage[i]);
+        if (c->stage_free[i]) cudaEventDestroy(c->stage_free[i]);
+    }
+    if (c->h_pairs) cudaFreeHost(c->h_pairs);
+    if (c->h_pair_out) cudaFreeHost(c->h_pair_out);
+    if (c->ev_upload) cudaEventDestroy(c->ev_upload);
+    if (c->ev_search) cudaEventDestroy(c->ev_search);
+    if (c->ev_k0) cudaEventDestroy(c->ev_k0);
+    if (c->ev_k1) cudaEventDestroy(c->ev_k1);
+    if (c->s_copy) cudaStreamDestroy(c->s_copy);
+    if (c->s_compute) cudaStreamDestroy(c->s_compute);
+    delete c;
+    return ME_OK;
+}
+
+int me_get_geometry(const me_ctx *c, me_geometry *g)
+{
+    if (!c || !g) return fail(ME_EINVAL, "NULL argument");
+    g->height = c->H; g->width = c->W;
+    g->nbx = c->args.nbx; g->nby = c->args.nby;
+    g->max_frames = c->max_frames; g->max_pairs = c->max_pairs;
+    g->tile_blocks_x = c->args.tbx; g->threads_per_cta = c->threads; g->smem_bytes = c->smem;
+    g->tiles_per_pair = c->args.tiles_per_pair;
+    g->cand_px_per_pair = c->cand_px; g->cand_px_per_pair_valid = c->cand_px_valid;
+    g->sm_count = c->sm_count; g->uses_tma = c->args.use_tma;
+    return ME_OK;
+}
+
+int me_upload(me_ctx *c, const uint8_t *luma, size_t row_pitch, int first_slot, int n_frames)
+{
+    if (!c) return fail(ME_EINVAL, "ctx is NULL");
+    return upload_impl(c, luma, row_pitch, first_slot, n_frames, false);
+}
+
+int me_upload_bgr(me_ctx *c, const uint8_t *bgr, size_t row_pitch, int first_slot, int n_frames)
+{
+    if (!c) return fail(ME_EINVAL, "ctx is NULL");
+    return upload_impl(c, bgr, row_pitch, first_slot, n_frames, true);
+}
+
+int me_search(me_ctx *c, const int32_t *pairs, int n_pairs)
+{
+    if (!c) return fail(ME_EINVAL, "ctx is NULL");
+    int rc = check_pairs(c, pairs, n_pairs, c->max_frames);
+    if (rc) return rc;
+    CU_TRY(cudaSetDevice(c->device));
+    if (c->have_search) CU_TRY(cudaEventSynchronize(c->ev_search));   // h_pairs is about to be rewritten
+    memcpy(c->h_pairs, pairs, sizeof(int32_t) * 2 * (size_t)n_pairs);
+    CU_TRY(cudaMemcpyAsync(c->d_pairs, c->h_pairs, sizeof(int32_t) * 2 * (size_t)n_pairs, cudaMemcpyHostToDevice, c->s_compute));
+    if (c->have_upload) CU_TRY(cudaStreamWaitEvent(c->s_compute, c->ev_upload, 0));
+    rc = launch_search(c, c->d_frames, c->tm_win, c->tm_ref, n_pairs, c->s_compute);
+    if (rc) return rc;
+    CU_TRY(cudaEventRecord(c->ev_search, c->s_compute));
+    c->have_search = true;
+    c->last_pairs = n_pairs;
+    return ME_OK;
+}
+
+int me_search_device(me_ctx *c, const uint8_t *d_frames, size_t pitch, int n_frames, const int32_t *pairs, int n_pairs,
+                     void *stream)
+{
+    if (!c) return fail(ME_EINVAL, "ctx is NULL");
+    if (!d_frames || (reinterpret_cast<uintptr_t>(d_frames) & 15) || pitch % 16 || pitch < (size_t)c->W)
+        return fail(ME_EINVAL, "device frames need a 16-byte aligned base and a pitch >= width that is a multiple of 16");
+    int rc = check_pairs(c, pairs, n_pairs, n_frames);
+    if (rc) return rc;
+    CU_TRY(cudaSetDevice(c->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : c->s_compute;
+    CUtensorMap tw, tr;
+    rc = make_tensor_map(&tw, d_frames, c->W, c->H, n_frames, pitch, c->args.win_pitch, c->args.box_rows);
+    if (!rc) rc = make_tensor_map(&tr, d_frames, c->W, c->H, n_frames, pitch, c->args.ref_pitch, c->p.block);
+    if (rc) return rc;
+    if (c->have_search) CU_TRY(cudaEventSynchronize(c->ev_search));
+    memcpy(c->h_pairs, pairs, sizeof(int32_t) * 2 * (size_t)n_pairs);
+    CU_TRY(cudaMemcpyAsync(c->d_pairs, c->h_pairs, sizeof(int32_t) * 2 * (size_t)n_pairs, cudaMemcpyHostToDevice, st));
+    const int keep_pitch = c->args.frame_pitch;
+    const long long keep_stride = c->args.frame_stride;
+    c->args.frame_pitch = (int)pitch;
+    c->args.frame_stride = (long long)pitch * c->H;
+    rc = launch_search(c, d_frames, tw, tr, n_pairs, st);
+    c->args.frame_pitch = keep_pitch;
+    c->args.frame_stride = keep_stride;
+    if (rc) return rc;
+    CU_TRY(cudaEventRecord(c->ev_search, st));
+    if (st != c->s_compute) CU_TRY(cudaStreamWaitEvent(c->s_compute, c->ev_search, 0));
+    c->have_search = true;
+    c->last_pairs = n_pairs;
+    return ME_OK;
+}
+
+int me_fetch_pairs(me_ctx *c, me_pair_result *out, int n_pairs)
+{
+    if (!c || !out) return fail(ME_EINVAL, "NULL argument");
+    if (!c->have_search) return fail(ME_ESTATE, "me_fetch_pairs before any me_search");
+    if (n_pairs < 1 || n_pairs > c->last_pairs) return fail(ME_EINVAL, "n_pairs=%d, last search had %d", n_pairs, c->last_pairs);
+    CU_TRY(cudaSetDevice(c->device));
+    CU_TRY(cudaMemcpyAsync(c->h_pair_out, c->args.pair_out, sizeof(me_pair_result) * (size_t)n_pairs,
+                           cudaMemcpyDeviceToHost, c->s_compute));
+    CU_TRY(cudaStreamSynchronize(c->s_compute));
+    memcpy(out, c->h_pair_out, sizeof(me_pair_result) * (size_t)n_pairs);
+    return ME_OK;
+}
+
+int me_fetch_blocks(me_ctx *c, int pair_index, int16_t *mv, uint32_t *sad, float *sub, uint8_t *flags)
+{
+    if (!c) return fail(ME_EINVAL, "ctx is NULL");
+    if (!c->have_search) return fail(ME_ESTATE, "me_fetch_blocks before any me_search");
+    if (pair_index < 0 || pair_index >= c->last_pairs) return fail(ME_EINVAL, "pair_index %d, last search had %d pairs", pair_index, c->last_pairs);
+    CU_TRY(cudaSetDevice(c->device));
+    const size_t nb = (size_t)c->args.nb, o = nb * (size_t)pair_index;
+    cudaStream_t st = c->s_compute;
+    if (mv) CU_TRY(cudaMemcpyAsync(mv, c->args.blk_mv + o * 2, nb * 2 * sizeof(int16_t), cudaMemcpyDeviceToHost, st));
+    if (sad) CU_TRY(cudaMemcpyAsync(sad, c->args.blk_sad + o, nb * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    if (sub) CU_TRY(cudaMemcpyAsync(sub, c->args.blk_sub + o * 2, nb * 2 * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (flags) CU_TRY(cudaMemcpyAsync(flags, c->args.blk_flags + o, nb, cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaStreamSynchronize(st));
+    return ME_OK;
+}
+
+int me_estimate_pair(me_ctx *c, const uint8_t *prev, const uint8_t *cur, size_t row_pitch, me_pair_result *out)
+{
+    if (!c || !prev || !cur || !out) return fail(ME_EINVAL, "NULL argument");
+    int rc = upload_impl(c, prev, row_pitch, 0, 1, false);
+    if (!rc) rc = upload_impl(c, cur, row_pitch, 1, 1, false);
+    const int32_t pr[2] = {0, 1};
+    if (!rc) rc = me_search(c, pr, 1);
+    if (!rc) rc = me_fetch_pairs(c, out, 1);
+    return rc;
+}
+
+int me_sync(me_ctx *c)
+{
+    if (!c) return fail(ME_EINVAL, "ctx is NULL");
+    CU_TRY(cudaSetDevice(c->device));
+    CU_TRY(cudaStreamSynchronize(c->s_copy));
+    CU_TRY(cudaStreamSynchronize(c->s_compute));
+    return ME_OK;
+}
+
+int me_last_search_ms(me_ctx *c, float *ms)
+{
+    if (!c || !ms) return fail(ME_EINVAL, "NULL argument");
+    if (!c->have_search) return fail(ME_ESTATE, "no search has been launched");
+    CU_TRY(cudaSetDevice(c->device));
+    CU_TRY(cudaEventSynchronize(c->ev_k1));
+    CU_TRY(cudaEventElapsedTime(ms, c->ev_k0, c->ev_k1));
+    return ME_OK;
+}
+
+int64_t me_launch_count(const me_ctx *c) { return c ? c->launches : 0; }
+
+int me_microbench_vabsdiff4(int device, int mode, double *instr_per_clk_per_sm, double *sm_mhz_seen, int *sm_count)
+{
+    if (!instr_per_clk_per_sm || !sm_mhz_seen || !sm_count) return fail(ME_EINVAL, "NULL argument");
+    CU_TRY(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU_TRY(cudaGetDeviceProperties(&prop, device));
+    const int sms = prop.multiProcessorCount, threads = 512, blocks = sms * 2, iters = 20000;
+    uint32_t *d_out = nullptr;
+    long long *d_clk = nullptr;
+    CU_TRY(cudaMalloc(&d_out, sizeof(uint32_t) * (size_t)blocks * threads));
+    CU_TRY(cudaMalloc(&d_clk, sizeof(long long) * (size_t)blocks));
+    cudaEvent_t e0, e1;
+    CU_TRY(cudaEventCreate(&e0));
+    CU_TRY(cudaEventCreate(&e1));
+    float ms = 0;
+    for (int rep = 0; rep < 3; ++rep) {           // the last repetition is the measurement
+        CU_TRY(cudaEventRecord(e0));
+        switch (mode) {
+        case 1: me::microbench_kernel<1><<<blocks, threads>>>(d_out, iters, d_clk, 12345u + rep); break;
+        case 2: me::microbench_kernel<2><<<blocks, threads>>>(d_out, iters, d_clk, 12345u + rep); break;
+        case 3: me::microbench_kernel<3><<<blocks, threads>>>(d_out, iters, d_clk, 12345u + rep); break;
+        default: me::microbench_kernel<0><<<blocks, threads>>>(d_out, iters, d_clk, 12345u + rep); break;
+        }
+        CU_TRY(cudaEventRecord(e1));
+        CU_TRY(cudaEventSynchronize(e1));
+        CU_TRY(cudaEventElapsedTime(&ms, e0, e1));
+    }
+    std::vector<long long> clk((size_t)blocks);
+    CU_TRY(cudaMemcpy(clk.data(), d_clk, sizeof(long long) * (size_t)blocks, cudaMemcpyDeviceToHost));
+    double mean_clk = 0;
+    for (long long v : clk) mean_clk += (double)v;
+    mean_clk /= blocks;
+    // two 512-thread CTAs share an SM for the whole run: per-SM thread-instructions / CTA clocks
+    const double instr_per_sm = 2.0 * threads * 16.0 * iters;
+    *instr_per_clk_per_sm = instr_per_sm / mean_clk;
+    *sm_mhz_seen = mean_clk / (ms * 1e3);
+    *sm_count = sms;
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(d_out); cudaFree(d_clk);
+    return ME_OK;
+}
+
+} // extern "C"

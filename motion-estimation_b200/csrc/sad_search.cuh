@@ -1,0 +1,577 @@
+// sad_search.cuh -- device side of the displacement search (sm_100a only).
+//
+// One CTA = one tile = `tbx` horizontally adjacent BxB blocks of the previous frame and the
+// (tbx*B + 2R) x (B + 2R) search window around them in the current frame.
+//
+//   staging   The window is brought into shared memory FOUR times by TMA, the s-th copy starting
+//             s bytes to the right (s = 0..3).  Candidate dx = 4q + s - R then reads only ALIGNED
+//             32-bit words of copy s, so the inner loop needs no byte realignment (no PRMT/SHF on
+//             the same pipe as the SAD op).  Out-of-frame bytes are zero-filled by TMA and the
+//             candidates that touch them are masked at argmin time (spec: in-frame domain only).
+//   inner     Each thread owns an NDY x NQ patch of candidates (same s, consecutive q, consecutive
+//             dy) and walks the window rows once; a current-frame word loaded into a register is
+//             used for up to NDY*min(NQ,BW) VABSDIFF4.U8.ACC ops, a reference word for NDY*NQ.
+//   argmin    key = (sad << rank_bits) | rank, rank = (dy+R)*(2R+1) + (dx+R): the minimum key is the
+//             first minimum in raster order whatever the reduction order (spec tie-break).
+//   finalize  one warp per block recomputes the four neighbour SADs from global memory, applies
+//             the parabola fit and the gates and writes the per-block record.
+//   reduce    the last CTA of a pair (atomic ticket) radix-selects the per-axis medians.
+//
+// The spec this implements is written down in oracle/sad_oracle.c; reference call sites replaced:
+// estimate_vel_vid.py:306-369 (calc_ECC_transform) and :522 (its caller).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/me_b200.h"
+
+namespace me {
+
+constexpr int kMaxTbx = 16;
+constexpr unsigned kFull = 0xffffffffu;
+
+struct SearchArgs {
+    // frames in device memory: (slots, H, pitch) uint8
+    const uint8_t *frames;
+    long long frame_stride;
+    int frame_pitch;
+    int W, H;
+    const int32_t *pairs;       // device, (prev, cur) x P
+    // block grid
+    int nbx, nby, nb;
+    int R, U;                   // U = 2R + 1
+    int tbx, tiles_x, tiles_per_pair;
+    // shared-memory window: 4 shifted copies, each alloc_rows x win_pitch bytes
+    int win_pitch, copy_bytes;
+    int box_rows, n_row_boxes;
+    int ref_pitch;              // tbx * B bytes
+    // candidate tiling
+    int ndyg;                   // ceil(U / NDY)
+    int cg_start[5];            // column groups of shift s are [cg_start[s], cg_start[s+1])
+    int per_j;                  // ndyg * cg_start[4] work items per block
+    // gates
+    int min_range, min_curv, subpixel, min_valid;
+    int rank_bits;
+    int use_tma;
+    // outputs
+    int16_t *blk_mv;            // [P][nb][2]
+    uint32_t *blk_sad;          // [P][nb]
+    float *blk_sub;             // [P][nb][2]
+    uint8_t *blk_flags;         // [P][nb]
+    me_pair_result *pair_out;   // [P]
+    unsigned int *pair_ticket;  // [P] scratch: zero on entry, reset to zero by the last CTA
+};
+
+// ---------------------------------------------------------------- PTX helpers
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ uint32_t vsad4(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t d;
+    asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;   // SASS: VABSDIFF4.U8.ACC
+}
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    uint32_t done, addr = smem_u32(bar);
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+    } while (!done);
+}
+// 3-D tiled TMA load (x, y, frame) -> shared; completes on the mbarrier.  SASS: UTMALDG.3D
+__device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *tm, int x, int y, int z, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+                 " [%0], [%1, {%2, %3, %4}], [%5];"
+                 ::"r"(smem_u32(dst)), "l"(tm), "r"(x), "r"(y), "r"(z), "r"(smem_u32(bar)) : "memory");
+}
+
+template <bool K64> struct KeyOf { using T = unsigned int; };
+template <> struct KeyOf<true> { using T = unsigned long long; };
+
+__device__ __forceinline__ unsigned int warp_min_key(unsigned int v) { return __reduce_min_sync(kFull, v); }
+__device__ __forceinline__ unsigned long long warp_min_key(unsigned long long v)
+{
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        unsigned long long t = __shfl_xor_sync(kFull, v, o);
+        v = t < v ? t : v;
+    }
+    return v;
+}
+
+// ---------------------------------------------------------------- inner loop
+// acc[d][q] += SAD over the BxB block for dy = dyg*NDY + d, q = qg*NQ + q (fixed shift s).
+//   cur : word pointer to copy s, row dyg*NDY, word j*BW + qg*NQ
+//   ref : word pointer to the reference tile, row 0, word j*BW
+template <int B, int NDY, int NQ>
+__device__ __forceinline__ void sad_patch(const uint32_t *__restrict__ cur, int cur_pitch_w,
+                                          const uint32_t *__restrict__ ref, int ref_pitch_w,
+                                          uint32_t (&acc)[NDY][NQ])
+{
+    constexpr int BW = B / 4;                       // words per block row
+    constexpr int NCW = NQ + BW - 1;                // current-frame words needed per window row
+    constexpr int LW = (BW % 4 == 0 && NQ % 4 == 0) ? 4 : ((BW % 2 == 0 && NQ % 2 == 0) ? 2 : 1);
+    constexpr int NLD = (NCW + LW - 1) / LW;
+    uint32_t refw[NDY][BW];                         // rotating window of the last NDY reference rows
+#pragma unroll
+    for (int yy = 0; yy < B + NDY - 1; ++yy) {
+        uint32_t cw[NLD * LW];
+        const uint32_t *crow = cur + yy * cur_pitch_w;
+#pragma unroll
+        for (int l = 0; l < NLD; ++l) {
+            if constexpr (LW == 4) {
+                uint4 v = *reinterpret_cast<const uint4 *>(crow + 4 * l);
+                cw[4 * l] = v.x; cw[4 * l + 1] = v.y; cw[4 * l + 2] = v.z; cw[4 * l + 3] = v.w;
+            } else if constexpr (LW == 2) {
+                uint2 v = *reinterpret_cast<const uint2 *>(crow + 2 * l);
+                cw[2 * l] = v.x; cw[2 * l + 1] = v.y;
+            } else {
+                cw[l] = crow[l];
+            }
+        }
+        if (yy < B) {
+            const uint32_t *rrow = ref + yy * ref_pitch_w;
+            if constexpr (BW % 4 == 0) {
+#pragma unroll
+                for (int l = 0; l < BW / 4; ++l) {
+                    uint4 v = *reinterpret_cast<const uint4 *>(rrow + 4 * l);
+                    refw[yy % NDY][4 * l] = v.x; refw[yy % NDY][4 * l + 1] = v.y;
+                    refw[yy % NDY][4 * l + 2] = v.z; refw[yy % NDY][4 * l + 3] = v.w;
+                }
+            } else {
+#pragma unroll
+                for (int l = 0; l < BW / 2; ++l) {
+                    uint2 v = *reinterpret_cast<const uint2 *>(rrow + 2 * l);
+                    refw[yy % NDY][2 * l] = v.x; refw[yy % NDY][2 * l + 1] = v.y;
+                }
+            }
+        }
+#pragma unroll
+        for (int d = 0; d < NDY; ++d) {
+            const int i = yy - d;                   // reference row paired with this window row for dy index d
+            if (i >= 0 && i < B) {
+#pragma unroll
+                for (int w = 0; w < BW; ++w)
+#pragma unroll
+                    for (int q = 0; q < NQ; ++q)
+                        acc[d][q] = vsad4(refw[i % NDY][w], cw[q + w], acc[d][q]);
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------- finalize helpers
+// 4 bytes from an arbitrary byte address, using aligned word loads only.  The second word is
+// touched only when it holds a needed byte, so an in-frame request never leaves its row pitch.
+__device__ __forceinline__ uint32_t ld_bytes4(const uint8_t *p)
+{
+    const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+    const uint32_t *q = reinterpret_cast<const uint32_t *>(a & ~uintptr_t(3));
+    const unsigned sh = (unsigned)(a & 3) * 8;
+    uint32_t lo = __ldg(q);
+    uint32_t hi = sh ? __ldg(q + 1) : 0u;
+    return __funnelshift_r(lo, hi, sh);
+}
+__device__ __forceinline__ uint32_t hmin_bytes(uint32_t v)
+{
+    return min(min(v & 255u, (v >> 8) & 255u), min((v >> 16) & 255u, v >> 24));
+}
+__device__ __forceinline__ uint32_t hmax_bytes(uint32_t v)
+{
+    return max(max(v & 255u, (v >> 8) & 255u), max((v >> 16) & 255u, v >> 24));
+}
+__device__ __forceinline__ uint32_t fkey(float f)      // order-preserving float -> uint
+{
+    uint32_t u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float funkey(uint32_t k)
+{
+    return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
+// One warp: neighbour SADs, gates, parabola, per-block record.
+template <int B>
+__device__ __forceinline__ void finalize_block(const SearchArgs &a, int pair, const uint8_t *prevf,
+                                               const uint8_t *curf, int bx, int by, uint32_t sad, uint32_t rank,
+                                               int lane)
+{
+    constexpr int BW = B / 4;
+    const int R = a.R, U = a.U, x0 = bx * B, y0 = by * B;
+    const int dyi = (int)(rank / (uint32_t)U), ui = (int)rank - dyi * U;
+    const int dx = ui - R, dy = dyi - R;
+    const int dxlo = max(-R, -x0), dxhi = min(R, a.W - B - x0);
+    const int dylo = max(-R, -y0), dyhi = min(R, a.H - B - y0);
+    const bool xin = dx - 1 >= dxlo && dx + 1 <= dxhi;
+    const bool yin = dy - 1 >= dylo && dy + 1 <= dyhi;
+    const size_t pitch = (size_t)a.frame_pitch;
+    uint32_t sxm = 0, sxp = 0, sym = 0, syp = 0, vmn = 0xffffffffu, vmx = 0u;
+    for (int idx = lane; idx < B * BW; idx += 32) {
+        const int row = idx / BW, wd = idx - row * BW;
+        const uint32_t rw = __ldg(reinterpret_cast<const uint32_t *>(prevf + (size_t)(y0 + row) * pitch + x0) + wd);
+        vmn = __vminu4(vmn, rw);
+        vmx = __vmaxu4(vmx, rw);
+        const uint8_t *c = curf + (size_t)(y0 + dy + row) * pitch + (x0 + dx + 4 * wd);
+        if (xin) {
+            sxm = vsad4(rw, ld_bytes4(c - 1), sxm);
+            sxp = vsad4(rw, ld_bytes4(c + 1), sxp);
+        }
+        if (yin) {
+            sym = vsad4(rw, ld_bytes4(c - pitch), sym);
+            syp = vsad4(rw, ld_bytes4(c + pitch), syp);
+        }
+    }
+    sxm = __reduce_add_sync(kFull, sxm);
+    sxp = __reduce_add_sync(kFull, sxp);
+    sym = __reduce_add_sync(kFull, sym);
+    syp = __reduce_add_sync(kFull, syp);
+    const uint32_t mn = __reduce_min_sync(kFull, hmin_bytes(vmn));
+    const uint32_t mx = __reduce_max_sync(kFull, hmax_bytes(vmx));
+    if (lane == 0) {
+        unsigned flags = 0;
+        if ((int)(mx - mn) >= a.min_range) flags |= ME_FLAG_TEXTURED;
+        float fx = (float)dx, fy = (float)dy;
+        const int c0 = (int)sad, mc = a.min_curv < 1 ? 1 : a.min_curv;
+        if (xin) {
+            flags |= ME_FLAG_X_INTERIOR;
+            const int den = (int)sxm - 2 * c0 + (int)sxp;
+            if (den >= mc) flags |= ME_FLAG_X_PEAKED;
+            if (den > 0 && a.subpixel)
+                fx = __fadd_rn(fx, __fmul_rn(0.5f, __fdiv_rn((float)((int)sxm - (int)sxp), (float)den)));
+        }
+        if (yin) {
+            flags |= ME_FLAG_Y_INTERIOR;
+            const int den = (int)sym - 2 * c0 + (int)syp;
+            if (den >= mc) flags |= ME_FLAG_Y_PEAKED;
+            if (den > 0 && a.subpixel)
+                fy = __fadd_rn(fy, __fmul_rn(0.5f, __fdiv_rn((float)((int)sym - (int)syp), (float)den)));
+        }
+        const size_t b = (size_t)pair * a.nb + (size_t)by * a.nbx + bx;
+        reinterpret_cast<short2 *>(a.blk_mv)[b] = make_short2((short)dx, (short)dy);
+        a.blk_sad[b] = sad;
+        reinterpret_cast<float2 *>(a.blk_sub)[b] = make_float2(fx, fy);
+        a.blk_flags[b] = (uint8_t)flags;
+        __threadfence();
+    }
+}
+
+// ---------------------------------------------------------------- per-pair median (last CTA)
+// k-th smallest key (0-based) among the axis' valid blocks by 4x8-bit MSB-first radix select.
+// Returns the key; *n_equal / *idx_in_equal describe the run of equal keys it sits in.
+__device__ uint32_t radix_select(const SearchArgs &a, int pair, int axis, unsigned need, unsigned k,
+                                 unsigned *hist, unsigned *bc, unsigned *n_equal, unsigned *idx_in_equal)
+{
+    const uint8_t *fl = a.blk_flags + (size_t)pair * a.nb;
+    const float *sub = a.blk_sub + (size_t)pair * a.nb * 2 + axis;
+    uint32_t prefix = 0, mask = 0;
+    for (int shift = 24; shift >= 0; shift -= 8) {
+        for (int i = threadIdx.x; i < 256; i += blockDim.x) hist[i] = 0;
+        __syncthreads();
+        for (int b = threadIdx.x; b < a.nb; b += blockDim.x) {
+            if ((__ldcg(fl + b) & need) == need) {
+                const uint32_t key = fkey(__ldcg(sub + 2 * b));
+                if ((key & mask) == prefix) atomicAdd(&hist[(key >> shift) & 255u], 1u);
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x < 32) {                     // warp 0: find the bin holding rank k
+            const int lane = threadIdx.x;
+            unsigned mine = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) mine += hist[lane * 8 + i];
+            unsigned incl = mine;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                unsigned t = __shfl_up_sync(kFull, incl, o);
+                if (lane >= o) incl += t;
+            }
+            const unsigned excl = incl - mine;
+            const bool has = k >= excl && k < incl;   // exactly one lane
+            if (has) {
+                unsigned cum = excl;
+                int sel = 0;
+                for (int i = 0; i < 8; ++i) {
+                    const unsigned h = hist[lane * 8 + i];
+                    if (k < cum + h) { sel = lane * 8 + i; break; }
+                    cum += h;
+                }
+                bc[0] = (unsigned)sel;
+                bc[1] = k - cum;                    // rank inside the chosen bin
+                bc[2] = hist[sel];
+            }
+        }
+        __syncthreads();
+        prefix |= bc[0] << shift;
+        mask |= 255u << shift;
+        k = bc[1];
+        if (shift == 0) { *n_equal = bc[2]; *idx_in_equal = bc[1]; }
+        __syncthreads();
+    }
+    return prefix;
+}
+
+__device__ void reduce_pair(const SearchArgs &a, int pair, unsigned *scratch)
+{
+    unsigned *hist = scratch;          // 256
+    unsigned *bc = scratch + 256;      // broadcast slots
+    const uint8_t *fl = a.blk_flags + (size_t)pair * a.nb;
+    const float *sub = a.blk_sub + (size_t)pair * a.nb * 2;
+    float med[2];
+    unsigned cnt[2];
+    for (int axis = 0; axis < 2; ++axis) {
+        const unsigned need = ME_FLAG_TEXTURED | (axis ? ME_FLAG_Y_PEAKED : ME_FLAG_X_PEAKED);
+        if (threadIdx.x == 0) { bc[4] = 0; bc[5] = 0xffffffffu; }
+        __syncthreads();
+        unsigned local = 0;
+        for (int b = threadIdx.x; b < a.nb; b += blockDim.x) local += ((__ldcg(fl + b) & need) == need);
+        local = __reduce_add_sync(kFull, local);
+        if ((threadIdx.x & 31) == 0 && local) atomicAdd(&bc[4], local);
+        __syncthreads();
+        const unsigned n = bc[4];
+        cnt[axis] = n;
+        med[axis] = 0.0f;
+        if (n == 0) { __syncthreads(); continue; }   // uniform across the CTA
+        const unsigned k1 = (n - 1) / 2, k2 = n / 2;
+        unsigned neq = 0, idx = 0;
+        const uint32_t v1 = radix_select(a, pair, axis, need, k1, hist, bc, &neq, &idx);
+        uint32_t v2 = v1;
+        if (k2 != k1 && idx + 1 >= neq) {           // upper middle is the next larger key
+            uint32_t best = 0xffffffffu;
+            for (int b = threadIdx.x; b < a.nb; b += blockDim.x)
+                if ((__ldcg(fl + b) & need) == need) {
+                    const uint32_t key = fkey(__ldcg(sub + 2 * b + axis));
+                    if (key > v1 && key < best) best = key;
+                }
+            best = __reduce_min_sync(kFull, best);
+            if ((threadIdx.x & 31) == 0) atomicMin(&bc[5], best);
+            __syncthreads();
+            v2 = bc[5];
+        }
+        med[axis] = __fmul_rn(0.5f, __fadd_rn(funkey(v1), funkey(v2)));
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        me_pair_result r;
+        r.pdx = med[0];
+        r.pdy = med[1];
+        r.flag = (int)cnt[0] >= (a.min_valid > 1 ? a.min_valid : 1);
+        r.nvalid_x = (int)cnt[0];
+        r.nvalid_y = (int)cnt[1];
+        r.reserved = 0;
+        a.pair_out[pair] = r;
+        a.pair_ticket[pair] = 0;                    // leave the scratch clean for the next launch
+    }
+}
+
+// ---------------------------------------------------------------- the search kernel
+template <int B, int NDY, int NQ, bool K64, int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT, MINB)
+sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_constant__ CUtensorMap tm_ref,
+                  const SearchArgs a)
+{
+    using KeyT = typename KeyOf<K64>::T;
+    constexpr int BW = B / 4;
+    constexpr KeyT kNone = ~KeyT(0);
+    extern __shared__ __align__(1024) uint8_t smem[];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    const int pair = blockIdx.x / a.tiles_per_pair;
+    const int tr = blockIdx.x - pair * a.tiles_per_pair;
+    const int ty = tr / a.tiles_x, tx = tr - ty * a.tiles_x;
+    const int prev_slot = __ldg(a.pairs + 2 * pair), cur_slot = __ldg(a.pairs + 2 * pair + 1);
+    const int X0 = tx * a.tbx * B, Y0 = ty * B;
+    const int nj = min(a.tbx, a.nbx - tx * a.tbx);
+
+    uint8_t *s_win = smem;
+    uint8_t *s_ref = smem + 4 * (size_t)a.copy_bytes + 256;            // 256 B of slack for tile over-reads
+    const int ref_bytes = (a.ref_pitch * B + 127) & ~127;
+    KeyT *s_key = reinterpret_cast<KeyT *>(s_ref + ref_bytes);         // [kMaxTbx]
+    uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_ref + ref_bytes + kMaxTbx * 8);
+    int *s_last = reinterpret_cast<int *>(s_bar + 1);
+
+    if (tid < kMaxTbx) s_key[tid] = kNone;
+
+    if (a.use_tma) {
+        if (tid == 0) mbar_init(s_bar, 1);
+        __syncthreads();
+        if (tid == 0) {
+            const uint32_t bytes = 4u * a.n_row_boxes * a.box_rows * a.win_pitch + (uint32_t)a.ref_pitch * B;
+            mbar_expect_tx(s_bar, bytes);
+            for (int s = 0; s < 4; ++s)
+                for (int rb = 0; rb < a.n_row_boxes; ++rb)
+                    tma_load_3d(s_win + (size_t)s * a.copy_bytes + (size_t)rb * a.box_rows * a.win_pitch, &tm_win,
+                                X0 - a.R + s, Y0 - a.R + rb * a.box_rows, cur_slot, s_bar);
+            tma_load_3d(s_ref, &tm_ref, X0, Y0, prev_slot, s_bar);
+        }
+        mbar_wait(s_bar, 0);
+    } else {
+        // Debug loader (ME_NO_TMA=1): same bytes with plain loads, zero outside the frame.
+        const uint8_t *curf = a.frames + (long long)cur_slot * a.frame_stride;
+        const uint8_t *prevf = a.frames + (long long)prev_slot * a.frame_stride;
+        const int rows = a.n_row_boxes * a.box_rows, per_copy = rows * a.win_pitch;
+        for (int i = tid; i < 4 * per_copy; i += blockDim.x) {
+            const int s = i / per_copy, o = i - s * per_copy, r = o / a.win_pitch, c = o - r * a.win_pitch;
+            const int gx = X0 - a.R + s + c, gy = Y0 - a.R + r;
+            uint8_t v = 0;
+            if (gx >= 0 && gx < a.W && gy >= 0 && gy < a.H) v = curf[(size_t)gy * a.frame_pitch + gx];
+            s_win[(size_t)s * a.copy_bytes + o] = v;
+        }
+        for (int i = tid; i < a.ref_pitch * B; i += blockDim.x) {
+            const int r = i / a.ref_pitch, c = i - r * a.ref_pitch;
+            const int gx = X0 + c, gy = Y0 + r;
+            s_ref[i] = (gx < a.W && gy < a.H) ? prevf[(size_t)gy * a.frame_pitch + gx] : 0;
+        }
+        __syncthreads();
+    }
+
+    // ---- candidate patches
+    const int total = nj * a.per_j;
+    const int iters = (total + (int)blockDim.x - 1) / (int)blockDim.x;
+    const int cur_pitch_w = a.win_pitch >> 2, ref_pitch_w = a.ref_pitch >> 2;
+    const int dyi_lo = max(0, a.R - Y0), dyi_hi = min(2 * a.R, a.R + a.H - B - Y0);
+    const KeyT scale = KeyT(1) << a.rank_bits;
+    for (int it = 0; it < iters; ++it) {
+        const int w_raw = it * (int)blockDim.x + tid;
+        const bool active = w_raw < total;
+        const int w = active ? w_raw : total - 1;
+        const int j = w / a.per_j, r = w - j * a.per_j;
+        const int cg = r / a.ndyg, dyg = r - cg * a.ndyg;       // dy group varies fastest across lanes
+        const int s = (cg >= a.cg_start[1]) + (cg >= a.cg_start[2]) + (cg >= a.cg_start[3]);
+        const int qg = cg - a.cg_start[s];
+        KeyT best = kNone;
+        if (active) {
+            uint32_t acc[NDY][NQ];
+#pragma unroll
+            for (int d = 0; d < NDY; ++d)
+#pragma unroll
+                for (int q = 0; q < NQ; ++q) acc[d][q] = 0;
+            const uint32_t *cur = reinterpret_cast<const uint32_t *>(s_win + (size_t)s * a.copy_bytes) +
+                                  dyg * NDY * cur_pitch_w + j * BW + qg * NQ;
+            const uint32_t *ref = reinterpret_cast<const uint32_t *>(s_ref) + j * BW;
+            sad_patch<B, NDY, NQ>(cur, cur_pitch_w, ref, ref_pitch_w, acc);
+
+            const int x0 = X0 + j * B;
+            const int u_lo = max(0, a.R - x0), u_hi = min(2 * a.R, a.R + a.W - B - x0);
+            const int dyi0 = dyg * NDY, u0 = 4 * qg * NQ + s;
+            const bool whole = dyi0 >= dyi_lo && dyi0 + NDY - 1 <= dyi_hi && u0 >= u_lo && u0 + 4 * (NQ - 1) <= u_hi;
+            const KeyT rank0 = (KeyT)(dyi0 * a.U + u0);
+            if (whole) {
+#pragma unroll
+                for (int d = 0; d < NDY; ++d)
+#pragma unroll
+                    for (int q = 0; q < NQ; ++q) {
+                        const KeyT key = (KeyT)acc[d][q] * scale + (rank0 + (KeyT)(d * a.U + 4 * q));
+                        best = key < best ? key : best;
+                    }
+            } else {
+#pragma unroll
+                for (int d = 0; d < NDY; ++d)
+#pragma unroll
+                    for (int q = 0; q < NQ; ++q) {
+                        const int dyi = dyi0 + d, u = u0 + 4 * q;
+                        const bool ok = dyi >= dyi_lo && dyi <= dyi_hi && u >= u_lo && u <= u_hi;
+                        const KeyT key = (KeyT)acc[d][q] * scale + (rank0 + (KeyT)(d * a.U + 4 * q));
+                        if (ok && key < best) best = key;
+                    }
+            }
+        }
+        // block-level argmin: one shared atomic per warp when the warp sits in one block
+        const int j0 = __shfl_sync(kFull, j, 0);
+        if (__all_sync(kFull, j == j0)) {
+            const KeyT m = warp_min_key(best);
+            if (lane == 0 && m != kNone) atomicMin(&s_key[j0], m);
+        } else if (best != kNone) {
+            atomicMin(&s_key[j], best);
+        }
+    }
+    __syncthreads();
+
+    // ---- per-block finalize (one warp per block)
+    {
+        const uint8_t *curf = a.frames + (long long)cur_slot * a.frame_stride;
+        const uint8_t *prevf = a.frames + (long long)prev_slot * a.frame_stride;
+        const KeyT rmask = scale - 1;
+        for (int j = warp; j < nj; j += nwarps) {
+            const KeyT key = s_key[j];
+            finalize_block<B>(a, pair, prevf, curf, tx * a.tbx + j, ty, (uint32_t)(key >> a.rank_bits),
+                              (uint32_t)(key & rmask), lane);
+        }
+    }
+    __syncthreads();
+
+    // ---- ticket: the last CTA of this pair reduces it
+    if (tid == 0) {
+        __threadfence();
+        const unsigned old = atomicAdd(&a.pair_ticket[pair], 1u);
+        *s_last = (old == (unsigned)a.tiles_per_pair - 1u);
+    }
+    __syncthreads();
+    if (*s_last) {
+        __threadfence();
+        reduce_pair(a, pair, reinterpret_cast<unsigned *>(s_win));
+    }
+}
+
+// ---------------------------------------------------------------- BGR -> luma (ingest, a9)
+// cv.cvtColor(BGR2GRAY) for 8-bit: Y = (B*1868 + G*9617 + R*4899 + 8192) >> 14.
+__global__ void bgr2gray_kernel(const uint8_t *__restrict__ bgr, size_t bgr_pitch, uint8_t *__restrict__ gray,
+                                size_t gray_pitch, int W, int rows)
+{
+    const int x4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const int y = blockIdx.y;
+    if (x4 >= W || y >= rows) return;
+    const uint8_t *p = bgr + (size_t)y * bgr_pitch + (size_t)x4 * 3;
+    uint8_t o[4] = {0, 0, 0, 0};
+    const int n = min(4, W - x4);
+    for (int i = 0; i < n; ++i)
+        o[i] = (uint8_t)((p[3 * i] * 1868u + p[3 * i + 1] * 9617u + p[3 * i + 2] * 4899u + 8192u) >> 14);
+    uint8_t *g = gray + (size_t)y * gray_pitch + x4;
+    if (n == 4) *reinterpret_cast<uchar4 *>(g) = make_uchar4(o[0], o[1], o[2], o[3]);
+    else for (int i = 0; i < n; ++i) g[i] = o[i];
+}
+
+// ---------------------------------------------------------------- issue-rate microbenchmark
+// mode 0: VABSDIFF4.U8.ACC only; 1: + one IADD3-class op per SAD op (same ALU pipe?);
+// mode 2: + one IMAD per SAD op (FMA pipe); 3: + one LDS.128 per 16 SAD ops.
+template <int MODE>
+__global__ void __launch_bounds__(512, 1) microbench_kernel(uint32_t *out, int iters, long long *clk, uint32_t seed)
+{
+    __shared__ uint4 sbuf[512];
+    sbuf[threadIdx.x] = make_uint4(seed, seed * 3u, seed * 5u, seed * 7u);
+    __syncthreads();
+    uint32_t acc[16], x = seed + threadIdx.x, y = seed * 2654435761u + blockIdx.x, z = 1;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) acc[i] = i;
+    long long t0 = clock64();
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            acc[i] = vsad4(x, y + i, acc[i]);
+            if (MODE == 1) z = (z + acc[(i + 8) & 15]) ^ x;
+            if (MODE == 2) z = z * 3u + x;
+        }
+        if (MODE == 3) { uint4 v = sbuf[(threadIdx.x + it) & 511]; x ^= v.x; y += v.y; z ^= v.z + v.w; }
+    }
+    long long t1 = clock64();
+    uint32_t s = z;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) s += acc[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+    if (threadIdx.x == 0) clk[blockIdx.x] = t1 - t0;
+}
+
+} // namespace me
