@@ -141,8 +141,8 @@ int64_t me_launch_count(const me_ctx *ctx);
 
 /* Integer-SAD issue-rate microbenchmark: runs a register-only VABSDIFF4 loop on every SM and
  * reports VABSDIFF4 thread-instructions per clock per SM and the SM clock it saw.  Used by bench.py
- * to put a measured number under the integer-ALU roofline.  mode 0 = SAD ops only; 1 = one extra
- * ALU-pipe op per SAD op; 2 = one extra FMA-pipe op (IMAD) per SAD op; 3 = one LDS.128 per 16. */
+ * to put a measured number under the integer-ALU roofline.  mode 0 = SAD ops only (a register 4x4
+ * patch, the search kernel's operand pattern); mode 1 adds one LDS.128 and 4 ALU ops per 16. */
 int me_microbench_vabsdiff4(int device, int mode, double *instr_per_clk_per_sm, double *sm_mhz_seen,
                             int *sm_count);
 

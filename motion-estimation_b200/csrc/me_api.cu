@@ -171,18 +171,21 @@ int configure(me_ctx *c)
 
     // Tile width: the widest tile whose window still fits one TMA box (<= 256 B) and leaves room for
     // >= 2 CTAs per SM; narrower when the frame is too small to fill the GPU otherwise.
+    // TMA needs a 16-byte aligned x origin; tiles start at multiples of 16, so the slack is fixed.
+    a.x_off = (16 - R % 16) % 16;
+    a.n_bufs = a.x_off ? 5 : 4;
     const int smem_cap = env_int("ME_SMEM_CAP", 100 * 1024);
     int best_tbx = 0;
     const int forced = env_int("ME_TBX", 0);
     for (int tbx = me::kMaxTbx; tbx >= 1; --tbx) {
         if ((tbx * B) % 16) continue;
         if (forced && tbx != forced) continue;
-        const int need = tbx * B + 2 * R;
+        const int need = a.x_off + tbx * B + 2 * R;
         int pitch = round_up(need, 16);
         if ((NDY & 1) && ((pitch / 16) & 1) == 0 && pitch + 16 <= 256) pitch += 16;   // odd 16-B pitch: conflict-free dy groups
         if (pitch > 256) continue;
         const int copy = round_up(alloc_rows * pitch, 128);
-        const int smem = 4 * copy + 256 + round_up(tbx * B * B, 128) + me::kMaxTbx * 8 + 64;
+        const int smem = a.n_bufs * copy + 256 + round_up(tbx * B * B, 128) + me::kMaxTbx * 8 + 64;
         if (smem > 227 * 1024) continue;
         const long long tiles = (long long)ceil_div(a.nbx, tbx) * a.nby;
         if (!forced) {
@@ -196,7 +199,7 @@ int configure(me_ctx *c)
     }
     if (!best_tbx)
         return fail(ME_EUNSUPPORTED, "block %d with range %d needs a %d-byte window row; one TMA box holds 256 "
-                    "(range <= %d for this block size)", B, R, B + 2 * R, (256 - B) / 2);
+                    "(range <= %d for this block size)", B, R, a.x_off + B + 2 * R, (256 - B) / 2);
     a.tiles_x = ceil_div(a.nbx, a.tbx);
     a.tiles_per_pair = a.tiles_x * a.nby;
 
@@ -556,7 +559,7 @@ int me_microbench_vabsdiff4(int device, int mode, double *instr_per_clk_per_sm, 
     CU_TRY(cudaSetDevice(device));
     cudaDeviceProp prop;
     CU_TRY(cudaGetDeviceProperties(&prop, device));
-    const int sms = prop.multiProcessorCount, threads = 512, blocks = sms * 2, iters = 20000;
+    const int sms = prop.multiProcessorCount, threads = 1024, blocks = sms, iters = 8192;
     uint32_t *d_out = nullptr;
     long long *d_clk = nullptr;
     CU_TRY(cudaMalloc(&d_out, sizeof(uint32_t) * (size_t)blocks * threads));
@@ -567,12 +570,8 @@ int me_microbench_vabsdiff4(int device, int mode, double *instr_per_clk_per_sm, 
     float ms = 0;
     for (int rep = 0; rep < 3; ++rep) {           // the last repetition is the measurement
         CU_TRY(cudaEventRecord(e0));
-        switch (mode) {
-        case 1: me::microbench_kernel<1><<<blocks, threads>>>(d_out, iters, d_clk, 12345u + rep); break;
-        case 2: me::microbench_kernel<2><<<blocks, threads>>>(d_out, iters, d_clk, 12345u + rep); break;
-        case 3: me::microbench_kernel<3><<<blocks, threads>>>(d_out, iters, d_clk, 12345u + rep); break;
-        default: me::microbench_kernel<0><<<blocks, threads>>>(d_out, iters, d_clk, 12345u + rep); break;
-        }
+        if (mode == 1) me::microbench_kernel<1><<<blocks, threads>>>(d_out, iters, d_clk, 12345u + rep);
+        else me::microbench_kernel<0><<<blocks, threads>>>(d_out, iters, d_clk, 12345u + rep);
         CU_TRY(cudaEventRecord(e1));
         CU_TRY(cudaEventSynchronize(e1));
         CU_TRY(cudaEventElapsedTime(&ms, e0, e1));
@@ -582,9 +581,8 @@ int me_microbench_vabsdiff4(int device, int mode, double *instr_per_clk_per_sm, 
     double mean_clk = 0;
     for (long long v : clk) mean_clk += (double)v;
     mean_clk /= blocks;
-    // two 512-thread CTAs share an SM for the whole run: per-SM thread-instructions / CTA clocks
-    const double instr_per_sm = 2.0 * threads * 16.0 * iters;
-    *instr_per_clk_per_sm = instr_per_sm / mean_clk;
+    // one 1024-thread CTA owns its SM for the whole run: thread-instructions / that CTA's clocks
+    *instr_per_clk_per_sm = (double)threads * 16.0 * iters / mean_clk;
     *sm_mhz_seen = mean_clk / (ms * 1e3);
     *sm_count = sms;
     cudaEventDestroy(e0); cudaEventDestroy(e1);

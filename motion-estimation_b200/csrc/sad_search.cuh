@@ -3,11 +3,14 @@
 // One CTA = one tile = `tbx` horizontally adjacent BxB blocks of the previous frame and the
 // (tbx*B + 2R) x (B + 2R) search window around them in the current frame.
 //
-//   staging   The window is brought into shared memory FOUR times by TMA, the s-th copy starting
-//             s bytes to the right (s = 0..3).  Candidate dx = 4q + s - R then reads only ALIGNED
-//             32-bit words of copy s, so the inner loop needs no byte realignment (no PRMT/SHF on
-//             the same pipe as the SAD op).  Out-of-frame bytes are zero-filled by TMA and the
-//             candidates that touch them are masked at argmin time (spec: in-frame domain only).
+//   staging   One TMA box brings the window into shared memory (x origin rounded down to 16 bytes:
+//             on this hardware a tiled TMA load faults unless its innermost coordinate is 16-byte
+//             aligned, measured with tools/probe/tma_probe.cu).  The CTA then derives FOUR copies
+//             of it, the s-th shifted s bytes to the left (s = 0..3, one SHF per word, <1 % of the
+//             SAD work).  Candidate dx = 4q + s - R then reads only ALIGNED 32-bit words of copy s,
+//             so the inner loop needs no byte realignment on the pipe the SAD op uses.
+//             Out-of-frame bytes are zero-filled by TMA and the candidates that touch them are
+//             masked at argmin time (spec: in-frame domain only).
 //   inner     Each thread owns an NDY x NQ patch of candidates (same s, consecutive q, consecutive
 //             dy) and walks the window rows once; a current-frame word loaded into a register is
 //             used for up to NDY*min(NQ,BW) VABSDIFF4.U8.ACC ops, a reference word for NDY*NQ.
@@ -44,6 +47,8 @@ struct SearchArgs {
     // shared-memory window: 4 shifted copies, each alloc_rows x win_pitch bytes
     int win_pitch, copy_bytes;
     int box_rows, n_row_boxes;
+    int x_off;                  // (X0 - R) - (16-byte aligned TMA x origin), 0..15
+    int n_bufs;                 // 4 when x_off == 0 (TMA lands in copy 0), else 5 (raw + 4 copies)
     int ref_pitch;              // tbx * B bytes
     // candidate tiling
     int ndyg;                   // ceil(U / NDY)
@@ -396,8 +401,9 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     const int X0 = tx * a.tbx * B, Y0 = ty * B;
     const int nj = min(a.tbx, a.nbx - tx * a.tbx);
 
-    uint8_t *s_win = smem;
-    uint8_t *s_ref = smem + 4 * (size_t)a.copy_bytes + 256;            // 256 B of slack for tile over-reads
+    uint8_t *s_win = smem;                                            // 4 shifted copies
+    uint8_t *s_raw = a.x_off ? smem + 4 * (size_t)a.copy_bytes : smem; // TMA destination
+    uint8_t *s_ref = smem + (size_t)a.n_bufs * a.copy_bytes + 256;    // 256 B of slack for tile over-reads
     const int ref_bytes = (a.ref_pitch * B + 127) & ~127;
     KeyT *s_key = reinterpret_cast<KeyT *>(s_ref + ref_bytes);         // [kMaxTbx]
     uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_ref + ref_bytes + kMaxTbx * 8);
@@ -405,16 +411,16 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
 
     if (tid < kMaxTbx) s_key[tid] = kNone;
 
+    const int wx0 = X0 - a.R - a.x_off;                               // multiple of 16
     if (a.use_tma) {
         if (tid == 0) mbar_init(s_bar, 1);
         __syncthreads();
         if (tid == 0) {
-            const uint32_t bytes = 4u * a.n_row_boxes * a.box_rows * a.win_pitch + (uint32_t)a.ref_pitch * B;
+            const uint32_t bytes = (uint32_t)a.n_row_boxes * a.box_rows * a.win_pitch + (uint32_t)a.ref_pitch * B;
             mbar_expect_tx(s_bar, bytes);
-            for (int s = 0; s < 4; ++s)
-                for (int rb = 0; rb < a.n_row_boxes; ++rb)
-                    tma_load_3d(s_win + (size_t)s * a.copy_bytes + (size_t)rb * a.box_rows * a.win_pitch, &tm_win,
-                                X0 - a.R + s, Y0 - a.R + rb * a.box_rows, cur_slot, s_bar);
+            for (int rb = 0; rb < a.n_row_boxes; ++rb)
+                tma_load_3d(s_raw + (size_t)rb * a.box_rows * a.win_pitch, &tm_win, wx0, Y0 - a.R + rb * a.box_rows,
+                            cur_slot, s_bar);
             tma_load_3d(s_ref, &tm_ref, X0, Y0, prev_slot, s_bar);
         }
         mbar_wait(s_bar, 0);
@@ -422,18 +428,49 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
         // Debug loader (ME_NO_TMA=1): same bytes with plain loads, zero outside the frame.
         const uint8_t *curf = a.frames + (long long)cur_slot * a.frame_stride;
         const uint8_t *prevf = a.frames + (long long)prev_slot * a.frame_stride;
-        const int rows = a.n_row_boxes * a.box_rows, per_copy = rows * a.win_pitch;
-        for (int i = tid; i < 4 * per_copy; i += blockDim.x) {
-            const int s = i / per_copy, o = i - s * per_copy, r = o / a.win_pitch, c = o - r * a.win_pitch;
-            const int gx = X0 - a.R + s + c, gy = Y0 - a.R + r;
+        const int rows = a.n_row_boxes * a.box_rows;
+        for (int i = tid; i < rows * a.win_pitch; i += blockDim.x) {
+            const int r = i / a.win_pitch, c = i - r * a.win_pitch;
+            const int gx = wx0 + c, gy = Y0 - a.R + r;
             uint8_t v = 0;
             if (gx >= 0 && gx < a.W && gy >= 0 && gy < a.H) v = curf[(size_t)gy * a.frame_pitch + gx];
-            s_win[(size_t)s * a.copy_bytes + o] = v;
+            s_raw[i] = v;
         }
         for (int i = tid; i < a.ref_pitch * B; i += blockDim.x) {
             const int r = i / a.ref_pitch, c = i - r * a.ref_pitch;
             const int gx = X0 + c, gy = Y0 + r;
             s_ref[i] = (gx < a.W && gy < a.H) ? prevf[(size_t)gy * a.frame_pitch + gx] : 0;
+        }
+        __syncthreads();
+    }
+
+    // ---- derive the byte-shifted copies: copy s, byte k of a row = raw byte (x_off + s + k)
+    {
+        const int chunks = a.n_row_boxes * a.box_rows * (a.win_pitch >> 4);   // 16-byte chunks per copy
+        const uint32_t *raw = reinterpret_cast<const uint32_t *>(s_raw);
+        for (int i = tid; i < chunks; i += blockDim.x) {
+            uint32_t w[9];
+            const uint4 v0 = *reinterpret_cast<const uint4 *>(raw + 4 * i);
+            const uint4 v1 = *reinterpret_cast<const uint4 *>(raw + 4 * i + 4);   // may run into the slack: unused bytes only
+            w[0] = v0.x; w[1] = v0.y; w[2] = v0.z; w[3] = v0.w; w[4] = v1.x; w[5] = v1.y; w[6] = v1.z; w[7] = v1.w;
+            w[8] = raw[4 * i + 8];
+#pragma unroll
+            for (int s = 0; s < 4; ++s) {
+                if (s == 0 && a.x_off == 0) continue;                 // copy 0 is the TMA destination itself
+                const int sh = a.x_off + s, wo = sh >> 2;
+                const unsigned bits = (unsigned)(sh & 3) * 8;
+                uint4 o;
+                // wo is 0..4 (x_off <= 15, s <= 3): select statically to keep w[] in registers
+                uint32_t e[5];
+#pragma unroll
+                for (int k = 0; k < 5; ++k)
+                    e[k] = wo == 0 ? w[k] : wo == 1 ? w[k + 1] : wo == 2 ? w[k + 2] : wo == 3 ? w[k + 3] : w[k + 4];
+                o.x = __funnelshift_r(e[0], e[1], bits);
+                o.y = __funnelshift_r(e[1], e[2], bits);
+                o.z = __funnelshift_r(e[2], e[3], bits);
+                o.w = __funnelshift_r(e[3], e[4], bits);
+                *reinterpret_cast<uint4 *>(s_win + (size_t)s * a.copy_bytes + 16 * (size_t)i) = o;
+            }
         }
         __syncthreads();
     }
@@ -545,29 +582,32 @@ __global__ void bgr2gray_kernel(const uint8_t *__restrict__ bgr, size_t bgr_pitc
 }
 
 // ---------------------------------------------------------------- issue-rate microbenchmark
-// mode 0: VABSDIFF4.U8.ACC only; 1: + one IADD3-class op per SAD op (same ALU pipe?);
-// mode 2: + one IMAD per SAD op (FMA pipe); 3: + one LDS.128 per 16 SAD ops.
+// Register-only 4x4 patch of VABSDIFF4.U8.ACC (the search kernel's operand pattern), one
+// 1024-thread CTA per SM.  MODE 1 adds one LDS.128 per 16 SAD ops (the kernel's load mix).
 template <int MODE>
-__global__ void __launch_bounds__(512, 1) microbench_kernel(uint32_t *out, int iters, long long *clk, uint32_t seed)
+__global__ void __launch_bounds__(1024, 1) microbench_kernel(uint32_t *out, int iters, long long *clk, uint32_t seed)
 {
-    __shared__ uint4 sbuf[512];
+    __shared__ uint4 sbuf[1024];
     sbuf[threadIdx.x] = make_uint4(seed, seed * 3u, seed * 5u, seed * 7u);
     __syncthreads();
-    uint32_t acc[16], x = seed + threadIdx.x, y = seed * 2654435761u + blockIdx.x, z = 1;
+    uint32_t acc[16], a[4], b[4];
 #pragma unroll
     for (int i = 0; i < 16; ++i) acc[i] = i;
-    long long t0 = clock64();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { a[i] = seed * (i + 1) + threadIdx.x; b[i] = seed ^ (i * 0x01010101u); }
+    const long long t0 = clock64();
     for (int it = 0; it < iters; ++it) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            acc[i] = vsad4(x, y + i, acc[i]);
-            if (MODE == 1) z = (z + acc[(i + 8) & 15]) ^ x;
-            if (MODE == 2) z = z * 3u + x;
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int d = 0; d < 4; ++d) acc[d * 4 + q] = vsad4(a[d], b[q], acc[d * 4 + q]);
+        if (MODE == 1) {
+            const uint4 v = sbuf[(threadIdx.x + it) & 1023];
+            b[0] ^= v.x; b[1] += v.y; b[2] ^= v.z; b[3] += v.w;
         }
-        if (MODE == 3) { uint4 v = sbuf[(threadIdx.x + it) & 511]; x ^= v.x; y += v.y; z ^= v.z + v.w; }
     }
-    long long t1 = clock64();
-    uint32_t s = z;
+    const long long t1 = clock64();
+    uint32_t s = 0;
 #pragma unroll
     for (int i = 0; i < 16; ++i) s += acc[i];
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;

@@ -55,7 +55,7 @@ def timing(H, W, B, R, P=16, reps=5):
 
 if __name__ == "__main__":
     print(me._lib.lib().me_version().decode())
-    for mode in range(4):
+    for mode in range(2):
         ipc, mhz, sms = me.microbench_vabsdiff4(0, mode)
         print(f"microbench mode {mode}: {ipc:.2f} VABSDIFF4 thread-instr/clk/SM at {mhz:.0f} MHz on {sms} SMs", flush=True)
     ok = True
