@@ -101,11 +101,13 @@ int me_get_geometry(const me_ctx *ctx, me_geometry *out);
  * where luma bytes exist.  Copies n_frames frames (row_pitch bytes between rows, frames contiguous:
  * frame f starts at luma + f*height*row_pitch) into the pinned staging ring and from there to device
  * slots first_slot.. with cudaMemcpyAsync on the copy stream.  Returns once the host buffer may be
- * reused; the device copy may still be in flight (me_search orders itself after it). */
+ * reused; the device copy may still be in flight (me_search orders itself after it).  A source that
+ * is already page-locked is copied directly, without the staging hop: it must then stay untouched
+ * until the next me_search / me_sync. */
 int me_upload(me_ctx *ctx, const uint8_t *luma, size_t row_pitch, int first_slot, int n_frames);
 
 /* Same for interleaved BGR frames as cv.VideoCapture delivers them (estimate_vel_vid.py:173-178):
- * the BGR2GRAY conversion runs on the GPU, bit-exact with cv.cvtColor's 14-bit fixed point. */
+ * the BGR2GRAY conversion runs on the GPU, bit-exact with cv.cvtColor's 15-bit fixed point. */
 int me_upload_bgr(me_ctx *ctx, const uint8_t *bgr, size_t row_pitch, int first_slot, int n_frames);
 
 /* Launch the search for n_pairs pairs of ring slots: pairs[2k] = previous frame, pairs[2k+1] =
@@ -138,6 +140,10 @@ int me_sync(me_ctx *ctx);
 int me_last_search_ms(me_ctx *ctx, float *ms);
 /* Number of kernels this context has launched so far (search, ingest conversion ...). */
 int64_t me_launch_count(const me_ctx *ctx);
+/* Device-side stopwatch on the context's compute stream (CUDA events): everything launched between
+ * start and stop.  me_timer_stop blocks until that work has finished. */
+int me_timer_start(me_ctx *ctx);
+int me_timer_stop(me_ctx *ctx, float *ms);
 
 /* Integer-SAD issue-rate microbenchmark: runs a register-only VABSDIFF4 loop on every SM and
  * reports VABSDIFF4 thread-instructions per clock per SM and the SM clock it saw.  Used by bench.py

@@ -92,13 +92,15 @@ def lib():
     L.me_search_device.argtypes = [vp, vp, C.c_size_t, C.c_int, i32p, C.c_int, vp]
     L.me_sync.argtypes = [vp]
     L.me_last_search_ms.argtypes = [vp, C.POINTER(C.c_float)]
+    L.me_timer_start.argtypes = [vp]
+    L.me_timer_stop.argtypes = [vp, C.POINTER(C.c_float)]
     L.me_launch_count.argtypes = [vp]
     L.me_launch_count.restype = C.c_int64
     L.me_microbench_vabsdiff4.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
                                           C.POINTER(C.c_int)]
     for name in ("me_create", "me_destroy", "me_get_geometry", "me_upload", "me_upload_bgr", "me_search",
                  "me_fetch_pairs", "me_fetch_blocks", "me_estimate_pair", "me_search_device", "me_sync",
-                 "me_last_search_ms", "me_microbench_vabsdiff4"):
+                 "me_last_search_ms", "me_microbench_vabsdiff4", "me_timer_start", "me_timer_stop"):
         getattr(L, name).restype = C.c_int
     _lib = L
     return L

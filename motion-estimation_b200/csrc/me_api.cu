@@ -121,6 +121,11 @@ struct me_ctx {
     cudaStream_t s_copy = nullptr, s_compute = nullptr;
     cudaEvent_t ev_upload = nullptr, ev_search = nullptr, ev_k0 = nullptr, ev_k1 = nullptr;
     bool have_upload = false, have_search = false;
+    cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;     // me_timer_start / me_timer_stop
+    // the last few searches and the ring slots they read: an upload waits only for those it overwrites
+    struct SearchRecord { int lo = 0, hi = -1; cudaEvent_t done = nullptr; bool used = false; };
+    SearchRecord recent[4];
+    int recent_next = 0;
     // pairs + results
     int32_t *h_pairs = nullptr, *d_pairs = nullptr;
     me_pair_result *h_pair_out = nullptr;
@@ -268,8 +273,22 @@ int upload_impl(me_ctx *c, const uint8_t *src, size_t row_pitch, int first_slot,
                     first_slot, c->max_frames);
     if (row_pitch < row_bytes) return fail(ME_EINVAL, "row_pitch %zu < %zu bytes per row", row_pitch, row_bytes);
     CU_TRY(cudaSetDevice(c->device));
-    if (c->have_search) CU_TRY(cudaStreamWaitEvent(c->s_copy, c->ev_search, 0));   // do not overwrite frames in use
+    for (auto &r : c->recent)                        // do not overwrite frames a running search still reads
+        if (r.used && r.lo < first_slot + n_frames && r.hi >= first_slot) CU_TRY(cudaStreamWaitEvent(c->s_copy, r.done, 0));
     const size_t frame_bytes = row_bytes * c->H;
+    // A source that is already page-locked (cudaHostAlloc / cudaHostRegister / torch pin_memory) is
+    // copied straight from where it lies; anything else goes through the pinned staging ring.
+    cudaPointerAttributes pa;
+    const bool pinned = cudaPointerGetAttributes(&pa, src) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+    if (!pinned) (void)cudaGetLastError();
+    if (pinned && !bgr) {
+        uint8_t *dst = c->d_frames + (size_t)first_slot * c->frame_stride;
+        CU_TRY(cudaMemcpy2DAsync(dst, c->pitch, src, row_pitch, row_bytes, (size_t)n_frames * c->H,
+                                 cudaMemcpyHostToDevice, c->s_copy));
+        CU_TRY(cudaEventRecord(c->ev_upload, c->s_copy));
+        c->have_upload = true;
+        return ME_OK;
+    }
     const int per_chunk = (int)(c->stage_bytes / frame_bytes);
     if (per_chunk < 1) return fail(ME_ENOMEM, "staging buffer smaller than one frame");
     for (int f = 0; f < n_frames; f += per_chunk) {
@@ -362,6 +381,9 @@ int me_create(int device, int height, int width, const me_params *params, int ma
     CREATE_TRY(cudaEventCreateWithFlags(&c->ev_search, cudaEventDisableTiming));
     CREATE_TRY(cudaEventCreate(&c->ev_k0));
     CREATE_TRY(cudaEventCreate(&c->ev_k1));
+    CREATE_TRY(cudaEventCreate(&c->ev_t0));
+    CREATE_TRY(cudaEventCreate(&c->ev_t1));
+    for (auto &r : c->recent) CREATE_TRY(cudaEventCreateWithFlags(&r.done, cudaEventDisableTiming));
     // staging: two buffers, each >= one BGR frame and about 32 MiB for long uploads
     size_t want = (size_t)width * height * 3;
     if (want < (32u << 20)) want = 32u << 20;
@@ -411,6 +433,9 @@ int me_destroy(me_ctx *c)
     if (c->ev_search) cudaEventDestroy(c->ev_search);
     if (c->ev_k0) cudaEventDestroy(c->ev_k0);
     if (c->ev_k1) cudaEventDestroy(c->ev_k1);
+    if (c->ev_t0) cudaEventDestroy(c->ev_t0);
+    if (c->ev_t1) cudaEventDestroy(c->ev_t1);
+    for (auto &r : c->recent) if (r.done) cudaEventDestroy(r.done);
     if (c->s_copy) cudaStreamDestroy(c->s_copy);
     if (c->s_compute) cudaStreamDestroy(c->s_compute);
     delete c;
@@ -455,6 +480,14 @@ int me_search(me_ctx *c, const int32_t *pairs, int n_pairs)
     rc = launch_search(c, c->d_frames, c->tm_win, c->tm_ref, n_pairs, c->s_compute);
     if (rc) return rc;
     CU_TRY(cudaEventRecord(c->ev_search, c->s_compute));
+    {
+        me_ctx::SearchRecord &r = c->recent[c->recent_next];
+        c->recent_next = (c->recent_next + 1) % 4;
+        r.lo = pairs[0]; r.hi = pairs[0];
+        for (int i = 0; i < 2 * n_pairs; ++i) { if (pairs[i] < r.lo) r.lo = pairs[i]; if (pairs[i] > r.hi) r.hi = pairs[i]; }
+        CU_TRY(cudaEventRecord(r.done, c->s_compute));
+        r.used = true;
+    }
     c->have_search = true;
     c->last_pairs = n_pairs;
     return ME_OK;
@@ -552,6 +585,24 @@ int me_last_search_ms(me_ctx *c, float *ms)
 }
 
 int64_t me_launch_count(const me_ctx *c) { return c ? c->launches : 0; }
+
+int me_timer_start(me_ctx *c)
+{
+    if (!c) return fail(ME_EINVAL, "ctx is NULL");
+    CU_TRY(cudaSetDevice(c->device));
+    CU_TRY(cudaEventRecord(c->ev_t0, c->s_compute));
+    return ME_OK;
+}
+
+int me_timer_stop(me_ctx *c, float *ms)
+{
+    if (!c || !ms) return fail(ME_EINVAL, "NULL argument");
+    CU_TRY(cudaSetDevice(c->device));
+    CU_TRY(cudaEventRecord(c->ev_t1, c->s_compute));
+    CU_TRY(cudaEventSynchronize(c->ev_t1));
+    CU_TRY(cudaEventElapsedTime(ms, c->ev_t0, c->ev_t1));
+    return ME_OK;
+}
 
 int me_microbench_vabsdiff4(int device, int mode, double *instr_per_clk_per_sm, double *sm_mhz_seen, int *sm_count)
 {

@@ -564,7 +564,7 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
 }
 
 // ---------------------------------------------------------------- BGR -> luma (ingest, a9)
-// cv.cvtColor(BGR2GRAY) for 8-bit: Y = (B*1868 + G*9617 + R*4899 + 8192) >> 14.
+// cv.cvtColor(BGR2GRAY) for 8-bit: Y = (B*3735 + G*19235 + R*9798 + 16384) >> 15 (cv2 4.13, checked in tests).
 __global__ void bgr2gray_kernel(const uint8_t *__restrict__ bgr, size_t bgr_pitch, uint8_t *__restrict__ gray,
                                 size_t gray_pitch, int W, int rows)
 {
@@ -575,7 +575,7 @@ __global__ void bgr2gray_kernel(const uint8_t *__restrict__ bgr, size_t bgr_pitc
     uint8_t o[4] = {0, 0, 0, 0};
     const int n = min(4, W - x4);
     for (int i = 0; i < n; ++i)
-        o[i] = (uint8_t)((p[3 * i] * 1868u + p[3 * i + 1] * 9617u + p[3 * i + 2] * 4899u + 8192u) >> 14);
+        o[i] = (uint8_t)((p[3 * i] * 3735u + p[3 * i + 1] * 19235u + p[3 * i + 2] * 9798u + 16384u) >> 15);
     uint8_t *g = gray + (size_t)y * gray_pitch + x4;
     if (n == 4) *reinterpret_cast<uchar4 *>(g) = make_uchar4(o[0], o[1], o[2], o[3]);
     else for (int i = 0; i < n; ++i) g[i] = o[i];

@@ -156,6 +156,14 @@ class MotionEstimator:
         check(self._L.me_last_search_ms(self._ctx, C.byref(ms)))
         return float(ms.value)
 
+    def timer_start(self):
+        check(self._L.me_timer_start(self._ctx))
+
+    def timer_stop(self) -> float:
+        ms = C.c_float()
+        check(self._L.me_timer_stop(self._ctx, C.byref(ms)))
+        return float(ms.value)
+
     def launch_count(self) -> int:
         return int(self._L.me_launch_count(self._ctx))
 

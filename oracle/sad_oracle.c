@@ -241,14 +241,16 @@ int me_oracle_search_pairs(const uint8_t *frames, int N, int H, int W, size_t pi
 
 /*
  * BGR -> luma exactly as cv.cvtColor(COLOR_BGR2GRAY) does it for 8-bit input
- * (reference call sites estimate_vel_vid.py:148,178): 14-bit fixed point,
- * Y = (B*1868 + G*9617 + R*4899 + 8192) >> 14.
+ * (reference call sites estimate_vel_vid.py:148,178): 15-bit fixed point,
+ * Y = (B*3735 + G*19235 + R*9798 + 16384) >> 15.  Pinned against the installed cv2 (4.13) in
+ * tests/test_oracle.py; the reference's own pin is opencv 4.6.0.66, whose coefficients cannot be
+ * checked offline.
  */
 int me_oracle_bgr2gray(const uint8_t *bgr, size_t npix, uint8_t *gray)
 {
     for (size_t i = 0; i < npix; ++i) {
         uint32_t b = bgr[3 * i], g = bgr[3 * i + 1], r = bgr[3 * i + 2];
-        gray[i] = (uint8_t)((b * 1868u + g * 9617u + r * 4899u + 8192u) >> 14);
+        gray[i] = (uint8_t)((b * 3735u + g * 19235u + r * 9798u + 16384u) >> 15);
     }
     return 0;
 }

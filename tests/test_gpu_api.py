@@ -1,0 +1,103 @@
+"""GPU tests of the drop-in layer: calc_ECC_transform / end_process with the reference's signatures,
+checked against the oracle (exact) and, softly, against what the reference's ECC produced on the
+example excerpts (tests/golden)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from oracle import sad as osad   # noqa: E402  (checker only)
+
+
+def test_calc_ecc_transform_signature_units_and_sign(me, golden_clips):
+    from motion_estimation_b200 import api
+    f = golden_clips["29.1"]["frames"]
+    pdx, pdy, flag = api.calc_ECC_transform(f[0], f[4])
+    o = osad.search(f[0], f[4], 16, 32)
+    assert flag == 1 and pdx == np.float32(o["pdx"] * np.float32(0.5)) and pdy == np.float32(o["pdy"] * np.float32(0.5))
+    fx, fy, _ = api.calc_ECC_transform(f[0], f[4], units="fullres")
+    assert (fx, fy) == (o["pdx"], o["pdy"])
+    assert api.calc_ECC_transform_raw(f[0], f[4]) == (o["pdx"], o["pdy"])
+    # +x content motion => pdx > 0, the sign the reference's ECC reports on this recording
+    assert pdx > 0 and golden_clips["29.1"]["ecc_ref"][12][0] > 0
+    before = f[0].copy()
+    api.calc_ECC_transform(f[0], f[1])
+    np.testing.assert_array_equal(f[0], before)              # inputs are never modified
+    api.close_engines()
+
+
+def test_displacements_agree_with_reference_ecc(me, golden_clips):
+    """Where the reference's ECC converged and the motion is inside +-32 px, the GPU result (already
+    halved to the reference's unit) is within 0.3 half-res px of it."""
+    from motion_estimation_b200 import api
+    n = 0
+    for name, g in golden_clips.items():
+        f = g["frames"]
+        for (a, b), want in zip(g["pairs"], g["ecc_ref"]):
+            if int(want[2]) != 1 or abs(want[0]) > 13:
+                continue
+            pdx, pdy, flag = api.calc_ECC_transform(f[a], f[b])
+            assert flag == 1 and abs(pdx - want[0]) < 0.3 and abs(pdy - want[1]) < 0.3, (name, a, b, pdx, want)
+            n += 1
+    assert n > 40
+    api.close_engines()
+
+
+@pytest.mark.parametrize("name", ["29.1", "58.2"])
+def test_end_process_equals_serial_oracle_loop(me, golden_clips, name):
+    """The batched, speculating end_process must return exactly what the serial anchor loop returns
+    when every pair goes through the oracle."""
+    from motion_estimation_b200 import api, velocity
+    g = golden_clips[name]
+    f, first = g["frames"], int(g["first"])
+    stamps = [0.0] * first + [float(t) for t in g["stamps_ms"]]
+
+    def pair(a, k):
+        o = osad.search(f[a], f[k], 16, 32)
+        h = np.float32(0.5)
+        return np.float32(o["pdx"] * h), np.float32(o["pdy"] * h), o["flag"]
+
+    lines = ["# timecode format v2"] + [repr(t) for t in stamps]
+    want = velocity.anchored_pair_loop(len(f), pair, velocity.timecode_lookup(lines), first_frame=first)
+    got = api.end_process(f, firstFrame=first, timestamps_ms=stamps, ring_frames=16, max_pairs=8, return_details=True)
+    assert got.accepted_pairs == want.accepted_pairs
+    assert got.out_information == want.out_information
+    assert got.motion_list_opt == want.motion_list_opt and got.tsList == want.tsList
+    tup = api.end_process(f, firstFrame=first, timestamps_ms=stamps)
+    assert len(tup) == 5 and tup[0] == want.out_information
+    api.close_engines()
+
+
+def test_end_process_tracks_reference_velocity_series(me, golden_clips):
+    """Against the reference's own end_process output on the 29.1 excerpt: same gate decisions on most
+    frames, and the travelled distance over the excerpt within 5 % (ECC is noisy at the 0.1 px level)."""
+    from motion_estimation_b200 import api
+    g = golden_clips["29.1"]
+    first = int(g["first"])
+    stamps = [0.0] * first + [float(t) for t in g["stamps_ms"]]
+    res = api.end_process(g["frames"], firstFrame=first, timestamps_ms=stamps, return_details=True)
+    ref_total = g["endproc_motion"][-1]
+    assert abs(res.motion_list_opt[-1] - ref_total) / ref_total < 0.05
+    assert abs(len(res.out_information) - len(g["endproc_out_information"])) <= 3
+    api.close_engines()
+
+
+def test_end_process_raw_flavour(me, golden_clips):
+    from motion_estimation_b200 import api
+    f = golden_clips["116.4"]["frames"][:12]
+    stamps = [int(round(t * 1000)) for t in golden_clips["116.4"]["stamps_ms"][:12]]
+    info, vx, vy, ts = api.end_process_raw(f, stamps, max_pairs=4)
+    assert len(info) == 11
+    o = osad.search(f[3], f[4], 16, 32)
+    t = stamps[4] / 10E+6
+    assert info[3] == ((float(o["pdx"]) / 611) / (t / 60), (float(o["pdy"]) / 611) / (t / 60), t)
+    api.close_engines()
+
+
+def test_dense_flow_mean(me, golden_clips):
+    from motion_estimation_b200 import api
+    f = golden_clips["29.1"]["frames"]
+    mx, my = api.calculate_dense_flow(f[5], f[6])
+    ref = golden_clips["29.1"]["flow_ref"][5]
+    assert mx > 5 and abs(my) < 1.5 and ref[0] > 0          # both see rightward motion; Farneback's mean is biased low
+    api.close_engines()

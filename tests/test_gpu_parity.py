@@ -1,0 +1,227 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (ctypes), against the C oracle.
+
+Integer displacements, SADs and flags must be bit-exact; the refined displacements and the pair
+medians are float32 computed with the same correctly-rounded operations in the same order, so they
+are compared for exact equality as well (tolerance 0; north_star allows 1e-3 px).
+At the sizes BASELINE.json names (1080p, 4K) the oracle is too slow to run on every block, so those
+cases use size-independent properties: known integer shifts recovered, batch-layout invariance, and
+oracle equality on a sample of blocks via the cost surface."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from oracle import sad as osad   # noqa: E402  (checker only)
+
+KEYS = ("mv", "sad", "sub", "flags")
+
+
+def check_pair(est, idx, prev, cur, cfg, rec):
+    o = osad.search(prev, cur, cfg.block, cfg.range, min_range=cfg.min_range, subpixel=cfg.subpixel,
+                    min_valid=cfg.min_valid, min_curv=cfg.min_curv)
+    g = est.fetch_blocks(idx)
+    for k in KEYS:
+        np.testing.assert_array_equal(g[k], o[k], err_msg=f"{k} (pair {idx})")
+    assert (rec["pdx"], rec["pdy"], rec["flag"], rec["nvalid_x"], rec["nvalid_y"]) == \
+           (o["pdx"], o["pdy"], o["flag"], o["nvalid_x"], o["nvalid_y"])
+
+
+CASES = [
+    # H, W, B, R   (ragged frames, every block size, ranges with and without 16-byte aligned origins)
+    (64, 96, 16, 8), (64, 640, 16, 32), (70, 100, 16, 8), (72, 200, 8, 12), (96, 160, 32, 16),
+    (270, 480, 16, 32), (136, 256, 8, 64), (48, 64, 16, 1), (33, 47, 16, 5), (64, 128, 32, 40),
+    (80, 144, 16, 50), (16, 16, 16, 4), (40, 336, 8, 7), (128, 128, 16, 100),
+]
+
+
+@pytest.mark.parametrize("H,W,B,R", CASES)
+def test_search_equals_oracle(me, H, W, B, R):
+    from motion_estimation_b200 import synth
+    n = 4
+    frames, _ = synth.translating_frames(n, H, W, min(R, 24))
+    cfg = me.SearchConfig(block=B, range=R)
+    with me.MotionEstimator(H, W, cfg, max_frames=n, max_pairs=n + 1) as est:
+        est.upload(frames)
+        pairs = [(0, 1), (1, 2), (2, 3), (3, 0), (2, 2)]
+        res = est.search(pairs)
+        for i, (a, c) in enumerate(pairs):
+            check_pair(est, i, frames[a], frames[c], cfg, res[i])
+
+
+@pytest.mark.parametrize("kw", [dict(subpixel=False), dict(min_range=60), dict(min_curv=400), dict(min_valid=10 ** 6)])
+def test_gates_and_modes_equal_oracle(me, kw):
+    from motion_estimation_b200 import synth
+    frames, _ = synth.translating_frames(3, 96, 160, 10)
+    cfg = me.SearchConfig(block=16, range=12, **kw)
+    with me.MotionEstimator(96, 160, cfg, max_frames=3, max_pairs=2) as est:
+        est.upload(frames)
+        res = est.search([(0, 1), (1, 2)])
+        for i in range(2):
+            check_pair(est, i, frames[i], frames[i + 1], cfg, res[i])
+    if "min_valid" in kw:
+        assert res[0]["flag"] == 0 and res[0]["nvalid_x"] > 0
+
+
+def test_ties_and_flat_frames_equal_oracle(me):
+    """Tie-break order is where parallel reductions usually go wrong: constant and periodic frames."""
+    flat = np.full((64, 96), 9, np.uint8)
+    per = np.tile(np.arange(8, dtype=np.uint8) * 20, (64, 12))
+    dark = np.zeros((64, 96), np.uint8)
+    dark[20:30, 40:50] = 200
+    frames = np.stack([flat, per, dark, np.roll(dark, 3, axis=1)])
+    cfg = me.SearchConfig(block=16, range=12, min_range=0)
+    with me.MotionEstimator(64, 96, cfg, max_frames=4, max_pairs=4) as est:
+        est.upload(frames)
+        pairs = [(0, 0), (1, 1), (2, 3), (0, 1)]
+        res = est.search(pairs)
+        for i, (a, c) in enumerate(pairs):
+            check_pair(est, i, frames[a], frames[c], cfg, res[i])
+
+
+def test_plain_loader_equals_tma_loader(me, monkeypatch):
+    """ME_NO_TMA=1 stages the window with ordinary loads; both stagings must give identical bytes."""
+    from motion_estimation_b200 import synth
+    frames, _ = synth.translating_frames(3, 80, 176, 16)
+    cfg = me.SearchConfig(block=16, range=20)
+    out = []
+    for flag in ("0", "1"):
+        monkeypatch.setenv("ME_NO_TMA", flag)
+        with me.MotionEstimator(80, 176, cfg, max_frames=3, max_pairs=2) as est:
+            assert est.geometry["uses_tma"] == (flag == "0")
+            est.upload(frames)
+            res = est.search([(0, 1), (1, 2)])
+            out.append((res.tobytes(), est.fetch_blocks(1)))
+    assert out[0][0] == out[1][0]
+    for k in KEYS:
+        np.testing.assert_array_equal(out[0][1][k], out[1][1][k])
+
+
+@pytest.mark.parametrize("tbx", [1, 2, 4, 8])
+def test_tile_width_does_not_change_results(me, monkeypatch, tbx):
+    from motion_estimation_b200 import synth
+    frames, _ = synth.translating_frames(2, 64, 208, 12)      # 13 blocks wide: ragged last tile for every tbx > 1
+    cfg = me.SearchConfig(block=16, range=16)
+    monkeypatch.setenv("ME_TBX", str(tbx))
+    with me.MotionEstimator(64, 208, cfg, max_frames=2, max_pairs=1) as est:
+        assert est.geometry["tile_blocks_x"] == tbx
+        est.upload(frames)
+        res = est.search([(0, 1)])
+        check_pair(est, 0, frames[0], frames[1], cfg, res[0])
+
+
+def test_example_recordings_equal_oracle(me, golden_clips):
+    """Every example sequence: integer displacements bit-exact against the oracle (north_star)."""
+    cfg = me.SearchConfig(block=16, range=32)
+    for name, g in golden_clips.items():
+        f = g["frames"]
+        with me.MotionEstimator(f.shape[1], f.shape[2], cfg, max_frames=len(f), max_pairs=64) as est:
+            est.upload(f)
+            pairs = [tuple(p) for p in g["pairs"]] + [(k, k + 1) for k in range(12, len(f) - 1)]
+            res = est.search(pairs)
+            for i, (a, c) in enumerate(pairs):
+                check_pair(est, i, f[a], f[c], cfg, res[i])
+            # and against the vectors committed with the excerpts
+            for (a, c), want, r in zip(g["pairs"], g["sad_pairs"], res):
+                assert [float(r["pdx"]), float(r["pdy"]), r["flag"], r["nvalid_x"], r["nvalid_y"]] == list(want)
+
+
+def test_estimate_pair_and_bgr_ingest(me, golden_clips):
+    f = golden_clips["58.2"]["frames"]
+    cfg = me.SearchConfig(block=8, range=12)
+    with me.MotionEstimator(64, 640, cfg, max_frames=4, max_pairs=2) as est:
+        r = est.estimate_pair(f[8], f[9])
+        o = osad.search(f[8], f[9], 8, 12)
+        assert (r["pdx"], r["pdy"], r["flag"], r["nvalid_x"]) == (o["pdx"], o["pdy"], o["flag"], o["nvalid_x"])
+        # BGR ingest: conversion on the GPU must equal cv.cvtColor, hence the same search result
+        import cv2
+        rng = np.random.default_rng(0)
+        bgr = rng.integers(0, 256, (2, 64, 640, 3), dtype=np.uint8)
+        bgr = np.stack([cv2.GaussianBlur(b, (0, 0), 2.0) for b in bgr])
+        gray = np.stack([cv2.cvtColor(b, cv2.COLOR_BGR2GRAY) for b in bgr])
+        est.upload_bgr(bgr, first_slot=2)
+        a = est.search([(2, 3)])
+        est.upload(gray, first_slot=0)
+        b = est.search([(0, 1)])
+        assert a.tobytes() == b.tobytes()
+        np.testing.assert_array_equal(gray[0], osad.bgr2gray(bgr[0]))
+
+
+def test_search_device_on_a_torch_tensor(me):
+    import torch
+    from motion_estimation_b200 import synth
+    frames, _ = synth.translating_frames(3, 64, 128, 10)
+    cfg = me.SearchConfig(block=16, range=12)
+    t = torch.from_numpy(frames).cuda().contiguous()
+    with me.MotionEstimator(64, 128, cfg, max_frames=2, max_pairs=2) as est:
+        n = est.search_device(t.data_ptr(), t.stride(1), t.shape[0], [(0, 1), (1, 2)],
+                              stream=torch.cuda.current_stream().cuda_stream)
+        res = est.fetch_pairs(n)
+        for i in range(2):
+            check_pair(est, i, frames[i], frames[i + 1], cfg, res[i])
+
+
+def test_errors_are_reported_not_swallowed(me):
+    with me.MotionEstimator(64, 128, me.SearchConfig(16, 8), max_frames=2, max_pairs=2) as est:
+        with pytest.raises(me.MEError):
+            est.fetch_pairs(1)                              # fetch before search
+        with pytest.raises(me.MEError):
+            est.launch([(0, 5)])                            # slot out of range
+        with pytest.raises(ValueError):
+            est.upload(np.zeros((1, 32, 128), np.uint8))    # wrong frame height
+    with pytest.raises(me.MEError) as e:
+        me.MotionEstimator(64, 128, me.SearchConfig(16, 128))
+    assert e.value.code == -2 and "range" in str(e.value)   # one TMA box per window: documented limit
+
+
+# ----------------------------------------------------------------------------- BASELINE sizes
+def _sample_blocks_equal_oracle(est, idx, prev, cur, B, R, blocks):
+    g = est.fetch_blocks(idx)
+    for bx, by in blocks:
+        cs = osad.cost_surface(prev, cur, B, R, bx, by).astype(np.int64)
+        rank = int(np.argmin(cs))
+        U = 2 * R + 1
+        assert tuple(g["mv"][by, bx]) == (rank % U - R, rank // U - R), (bx, by)
+        assert g["sad"][by, bx] == cs.flat[rank]
+
+
+def test_full_hd_properties(me):
+    """configs[2]: 1920x1080, B=16, R=32.  Known integer shifts recovered exactly (integer mode),
+    sampled blocks equal the oracle, and results do not depend on batch layout."""
+    from motion_estimation_b200 import synth
+    n = 5
+    frames, shifts = synth.translating_frames(n, 1080, 1920, 32)
+    cfg = me.SearchConfig(block=16, range=32, subpixel=False)
+    with me.MotionEstimator(1080, 1920, cfg, max_frames=n, max_pairs=n) as est:
+        est.upload(frames)
+        pairs = [(k, k + 1) for k in range(n - 1)]
+        res = est.search(pairs)
+        keep = [est.fetch_blocks(i) for i in range(len(pairs))]
+        for i, (dx, dy) in enumerate(shifts):
+            assert res[i]["flag"] == 1 and res[i]["pdx"] == dx and res[i]["pdy"] == dy
+            inner = keep[i]["mv"][3:-3, 3:-3]
+            assert (inner[..., 0] == dx).all() and (inner[..., 1] == dy).all()
+            assert (keep[i]["sad"][3:-3, 3:-3] == 0).all()
+        _sample_blocks_equal_oracle(est, 0, frames[0], frames[1], 16, 32,
+                                    [(0, 0), (119, 66), (1, 65), (60, 33), (118, 0), (0, 66), (59, 1)])
+        # same pairs one at a time, in reverse order: identical records and blocks
+        for i in reversed(range(len(pairs))):
+            one = est.search([pairs[i]])
+            assert one[0].tobytes() == res[i].tobytes()
+            b = est.fetch_blocks(0)
+            for k in KEYS:
+                np.testing.assert_array_equal(b[k], keep[i][k])
+
+
+def test_4k_properties(me):
+    """configs[3]: 3840x2160, B=8, R=64."""
+    from motion_estimation_b200 import synth
+    frames, shifts = synth.translating_frames(3, 2160, 3840, 64)
+    cfg = me.SearchConfig(block=8, range=64, subpixel=False)
+    with me.MotionEstimator(2160, 3840, cfg, max_frames=3, max_pairs=2) as est:
+        est.upload(frames)
+        res = est.search([(0, 1), (1, 2)])
+        for i, (dx, dy) in enumerate(shifts):
+            assert res[i]["flag"] == 1 and res[i]["pdx"] == dx and res[i]["pdy"] == dy
+        _sample_blocks_equal_oracle(est, 1, frames[1], frames[2], 8, 64, [(0, 0), (479, 269), (240, 135), (7, 262)])
