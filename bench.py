@@ -266,7 +266,7 @@ def run_ours(args):
         "wall_ms_per_step": wall_ms_step,
         "roofline": roofline,
         "cpu_baseline": cpu,
-        "results_checked": ok,
+        "results_checked": bool(ok),
         "velocity_mm_min_first3": [float(v) for v in vel[0][:3]],
     }
     print(json.dumps(line))

@@ -32,7 +32,7 @@ CASES = [
     # H, W, B, R   (ragged frames, every block size, ranges with and without 16-byte aligned origins)
     (64, 96, 16, 8), (64, 640, 16, 32), (70, 100, 16, 8), (72, 200, 8, 12), (96, 160, 32, 16),
     (270, 480, 16, 32), (136, 256, 8, 64), (48, 64, 16, 1), (33, 47, 16, 5), (64, 128, 32, 40),
-    (80, 144, 16, 50), (16, 16, 16, 4), (40, 336, 8, 7), (128, 128, 16, 100),
+    (80, 144, 16, 50), (16, 16, 16, 4), (40, 336, 8, 7), (128, 128, 16, 96),
 ]
 
 
