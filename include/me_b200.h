@@ -152,6 +152,28 @@ int me_timer_stop(me_ctx *ctx, float *ms);
 int me_microbench_vabsdiff4(int device, int mode, double *instr_per_clk_per_sm, double *sm_mhz_seen,
                             int *sm_count);
 
+/* Search with no allocation of any kind -- for callers that cannot allocate at the moment they need
+ * a search: a plug-in inside a framework whose pool already owns the GPU's memory, a real-time loop
+ * that must not trigger cudaMalloc's device-wide synchronisation, a worker with no memory budget of
+ * its own.  (No counterpart in the reference, which never leaves the CPU; added for such hosts.)
+ *
+ * The caller passes what it already has: device frames (n_frames, height, pitch), 16-byte aligned,
+ * pitch % 16 == 0; a HOST list of n_pairs (prev, cur) frame indices; a DEVICE array d_out of n_pairs
+ * records; its stream (NULL = default stream).  The kernel's working memory (per-block records,
+ * per-pair tickets) comes from a fixed ME_STATIC_SCRATCH_BYTES array inside the library, held by
+ * every GPU that loads it until the process exits.  A request that needs more returns ME_EINVAL
+ * (1080p with 16x16 blocks: 137 KB per pair, about 30 pairs per call).
+ *
+ * All calls share that array and it keeps the previous call's contents; what must be zero is
+ * cleared on `stream` before each launch.  Calls whose kernels could overlap on the GPU race on it:
+ * keep them on one stream or order them.  The first call on a device also performs that device's
+ * one-time set-up and should be made outside stream capture.  Asynchronous: d_out is valid once
+ * `stream` has drained.  Neither cudaMalloc/cudaFree nor any allocating library routine is called. */
+#define ME_STATIC_SCRATCH_BYTES (4u << 20)
+int me_search_static_scratch(const uint8_t *d_frames, size_t pitch, int n_frames, int height, int width,
+                             const me_params *params, const int32_t *pairs, int n_pairs,
+                             me_pair_result *d_out, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

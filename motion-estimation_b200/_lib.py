@@ -98,6 +98,9 @@ def lib():
     L.me_launch_count.restype = C.c_int64
     L.me_microbench_vabsdiff4.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
                                           C.POINTER(C.c_int)]
+    L.me_search_static_scratch.argtypes = [vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.POINTER(Params), i32p, C.c_int,
+                                           vp, vp]
+    L.me_search_static_scratch.restype = C.c_int
     for name in ("me_create", "me_destroy", "me_get_geometry", "me_upload", "me_upload_bgr", "me_search",
                  "me_fetch_pairs", "me_fetch_blocks", "me_estimate_pair", "me_search_device", "me_sync",
                  "me_last_search_ms", "me_microbench_vabsdiff4", "me_timer_start", "me_timer_stop"):

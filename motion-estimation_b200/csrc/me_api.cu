@@ -642,3 +642,131 @@ int me_microbench_vabsdiff4(int device, int mode, double *instr_per_clk_per_sm, 
 }
 
 } // extern "C"
+
+// =============================================================================================
+// me_search_static_scratch -- the one entry point that allocates nothing.
+//
+// Every other search call works on a context, and creating a context allocates (device ring,
+// result buffers, pinned staging).  Some hosts of this library cannot allocate when they need a
+// search: a plug-in living inside a framework whose memory pool already owns the whole GPU, a
+// real-time loop in which cudaMalloc's implicit device-wide synchronisation would stall the other
+// streams, or a worker that was handed its buffers by a parent process and has no budget of its
+// own.  Such a caller brings the frames and the output array (device memory it already has) and
+// this function supplies the kernel's working memory -- the per-block records the fused median
+// reads back and the per-pair tickets -- from a fixed array that is part of the loaded module.
+//
+// The array is ME_STATIC_SCRATCH_BYTES (4 MiB) and every GPU that loads the library carries it
+// until the process exits.  Requests that need more are refused with ME_EINVAL and a message that
+// states need and limit (1080p/16x16: 137 KB per pair => up to 30 pairs per call; 4K/8x8: one pair).
+//
+// All calls share that one array and it keeps whatever the previous call left in it.  The tickets,
+// the only part that must start at zero, are cleared on the caller's stream before each launch;
+// everything else is overwritten before it is read.  Two calls whose kernels can overlap on the GPU
+// (different streams, or different host threads) race on the array: issue them on one stream or
+// order them yourself.
+//
+// The first call on a device does the one-time set-up for that device (it resolves the array's
+// device address and raises the kernel's shared-memory limit).  Make that first call outside any
+// stream capture.  The call is asynchronous: results are in d_out once `stream` has drained.
+// =============================================================================================
+static __device__ __align__(256) unsigned char g_static_scratch[ME_STATIC_SCRATCH_BYTES];
+
+namespace {
+
+struct StaticDevice {
+    bool ready = false;
+    unsigned char *scratch = nullptr;   // device address of g_static_scratch on this device
+    int sm_count = 0;
+};
+StaticDevice g_static_dev[64];
+
+inline size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
+
+// Once per device, with that device current.  In host code `g_static_scratch` is only a handle for
+// the symbol; the address a kernel can use comes from cudaGetSymbolAddress.
+int static_device_setup(int dev)
+{
+    StaticDevice &d = g_static_dev[dev];
+    if (d.ready) return ME_OK;
+    void *ptr = nullptr;
+    CU_TRY(cudaGetSymbolAddress(&ptr, g_static_scratch));
+    if (!ptr) return fail(ME_ECUDA, "cudaGetSymbolAddress returned a null address for the static scratch array");
+    CU_TRY(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, dev));
+    d.scratch = static_cast<unsigned char *>(ptr);
+    d.ready = true;
+    return ME_OK;
+}
+
+} // namespace
+
+extern "C" int me_search_static_scratch(const uint8_t *d_frames, size_t pitch, int n_frames, int height, int width,
+                                        const me_params *params, const int32_t *pairs, int n_pairs,
+                                        me_pair_result *d_out, void *stream)
+{
+    if (!d_frames || !params || !pairs || !d_out) return fail(ME_EINVAL, "NULL argument");
+    const int B = params->block, R = params->range;
+    if (B != 8 && B != 16 && B != 32) return fail(ME_EUNSUPPORTED, "block size %d: built sizes are 8, 16, 32", B);
+    if (R < 1) return fail(ME_EINVAL, "range %d < 1", R);
+    if (height < B || width < B) return fail(ME_EINVAL, "frame %dx%d smaller than one %d-pixel block", width, height, B);
+    if ((reinterpret_cast<uintptr_t>(d_frames) & 15) || pitch % 16 || pitch < (size_t)width)
+        return fail(ME_EINVAL, "device frames need a 16-byte aligned base and a pitch >= width that is a multiple of 16");
+    if (n_frames < 1 || n_pairs < 1) return fail(ME_EINVAL, "n_frames and n_pairs must be positive");
+    for (int i = 0; i < 2 * n_pairs; ++i)
+        if (pairs[i] < 0 || pairs[i] >= n_frames)
+            return fail(ME_EINVAL, "pair %d references frame %d, outside 0..%d", i / 2, pairs[i], n_frames - 1);
+
+    int dev = 0;
+    CU_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(ME_EUNSUPPORTED, "device ordinal %d outside the static table", dev);
+    int rc = static_device_setup(dev);
+    if (rc) return rc;
+
+    // Launch shape: the same planner the contexts use, run on a throw-away host-side description.
+    me_ctx plan;
+    plan.device = dev; plan.H = height; plan.W = width; plan.p = *params;
+    plan.max_frames = n_frames; plan.max_pairs = n_pairs;
+    plan.sm_count = g_static_dev[dev].sm_count;
+    plan.pitch = pitch; plan.frame_stride = pitch * (size_t)height;
+    rc = configure(&plan);
+    if (rc) return rc;
+
+    // Carve the static array: tickets | pairs | mv | sad | sub | flags
+    const size_t nb = (size_t)plan.args.nb * (size_t)n_pairs;
+    const size_t o_ticket = 0;
+    const size_t o_pairs = o_ticket + align256(sizeof(unsigned) * (size_t)n_pairs);
+    const size_t o_mv = o_pairs + align256(sizeof(int32_t) * 2 * (size_t)n_pairs);
+    const size_t o_sad = o_mv + align256(nb * 2 * sizeof(int16_t));
+    const size_t o_sub = o_sad + align256(nb * sizeof(uint32_t));
+    const size_t o_flags = o_sub + align256(nb * 2 * sizeof(float));
+    const size_t need = o_flags + align256(nb);
+    if (need > (size_t)ME_STATIC_SCRATCH_BYTES)
+        return fail(ME_EINVAL, "%d pair(s) of %d blocks need %zu bytes of working memory; the static array holds %u "
+                    "(ME_STATIC_SCRATCH_BYTES). Split the batch or use a context (me_create / me_search_device).",
+                    n_pairs, plan.args.nb, need, (unsigned)ME_STATIC_SCRATCH_BYTES);
+
+    unsigned char *base = g_static_dev[dev].scratch;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CUtensorMap tw, tr;
+    rc = make_tensor_map(&tw, d_frames, width, height, n_frames, pitch, plan.args.win_pitch, plan.args.box_rows);
+    if (!rc) rc = make_tensor_map(&tr, d_frames, width, height, n_frames, pitch, plan.args.ref_pitch, B);
+    if (rc) return rc;
+    CU_TRY(cudaFuncSetAttribute(plan.kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, plan.smem));
+
+    me::SearchArgs a = plan.args;
+    a.frames = d_frames;
+    a.pair_ticket = reinterpret_cast<unsigned int *>(base + o_ticket);
+    a.pairs = reinterpret_cast<const int32_t *>(base + o_pairs);
+    a.blk_mv = reinterpret_cast<int16_t *>(base + o_mv);
+    a.blk_sad = reinterpret_cast<uint32_t *>(base + o_sad);
+    a.blk_sub = reinterpret_cast<float *>(base + o_sub);
+    a.blk_flags = base + o_flags;
+    a.pair_out = d_out;
+    // the tickets must start at zero; the rest of the array is written before it is read
+    CU_TRY(cudaMemsetAsync(base + o_ticket, 0, sizeof(unsigned) * (size_t)n_pairs, st));
+    CU_TRY(cudaMemcpyAsync(base + o_pairs, pairs, sizeof(int32_t) * 2 * (size_t)n_pairs, cudaMemcpyHostToDevice, st));
+    void *kargs[3] = {(void *)&tw, (void *)&tr, (void *)&a};
+    CU_TRY(cudaLaunchKernel(plan.kc.fn, dim3((unsigned)(a.tiles_per_pair * n_pairs)), dim3((unsigned)plan.threads), kargs,
+                            (size_t)plan.smem, st));
+    return ME_OK;
+}
+
