@@ -91,7 +91,7 @@ KernelChoice pick_kernel(int B, bool k64)
     switch (B) {
     case 8:  return k64 ? choice<8, 5, 8, true, 512, 1>() : choice<8, 5, 8, false, 512, 1>();
     case 16: return k64 ? choice<16, 5, 4, true, 512, 1>() : choice<16, 5, 4, false, 512, 1>();
-    default: return k64 ? choice<32, 4, 4, true, 512, 1>() : choice<32, 4, 4, false, 512, 1>();
+    default: return k64 ? choice<32, 5, 4, true, 512, 1>() : choice<32, 5, 4, false, 512, 1>();
     }
 }
 
@@ -179,16 +179,23 @@ int configure(me_ctx *c)
     // TMA needs a 16-byte aligned x origin; tiles start at multiples of 16, so the slack is fixed.
     a.x_off = (16 - R % 16) % 16;
     a.n_bufs = a.x_off ? 5 : 4;
-    const int smem_cap = env_int("ME_SMEM_CAP", 100 * 1024);
+    const int smem_cap = env_int("ME_SMEM_CAP", 72 * 1024);
     int best_tbx = 0;
     const int forced = env_int("ME_TBX", 0);
+    // Shared-memory banks: the 8 lanes of a quarter-warp read 16 bytes each from rows NDY apart, so the
+    // row pitch in 16-byte units times NDY must be odd for them to land in 8 different bank groups
+    // (r01 ncu: a 256-byte pitch cost 5.4 wavefronts per LDS.128 and made the kernel smem-bound).
+    // Pass 0 accepts only such pitches, pass 1 anything that fits.
+    for (int pass = 0; pass < 2 && !best_tbx; ++pass)
     for (int tbx = me::kMaxTbx; tbx >= 1; --tbx) {
         if ((tbx * B) % 16) continue;
         if (forced && tbx != forced) continue;
         const int need = a.x_off + tbx * B + 2 * R;
         int pitch = round_up(need, 16);
-        if ((NDY & 1) && ((pitch / 16) & 1) == 0 && pitch + 16 <= 256) pitch += 16;   // odd 16-B pitch: conflict-free dy groups
+        if ((NDY & 1) && ((pitch / 16) & 1) == 0 && pitch + 16 <= 256) pitch += 16;
         if (pitch > 256) continue;
+        const bool conflict_free = ((NDY * (pitch / 16)) & 1) != 0;
+        if (pass == 0 && !conflict_free && !forced) continue;
         const int copy = round_up(alloc_rows * pitch, 128);
         const int smem = a.n_bufs * copy + 256 + round_up(tbx * B * B, 128) + me::kMaxTbx * 8 + 64;
         if (smem > 227 * 1024) continue;
@@ -208,14 +215,15 @@ int configure(me_ctx *c)
     a.tiles_x = ceil_div(a.nbx, a.tbx);
     a.tiles_per_pair = a.tiles_x * a.nby;
 
-    // Threads: a multiple of 32 that wastes the fewest lanes on a full tile.
+    // Threads: whole multiples of 4 warps so that every scheduler of the SM gets the same number of warps
+    // (r01 sweep: 224 threads = 7 warps ran 13 % slower than 128 or 256), then fewest idle lanes.
     const int total = a.tbx * a.per_j;
     int best_t = 128;
     double best_eff = -1;
     const int tmax = env_int("ME_THREADS_MAX", 256);
-    for (int t = 128; t <= tmax && t <= c->kc.maxt; t += 32) {
+    for (int t = 128; t <= tmax && t <= c->kc.maxt; t += 128) {
         const double eff = (double)total / ((double)ceil_div(total, t) * t);
-        if (eff >= best_eff - 1e-9) { best_eff = eff; best_t = t; }
+        if (eff >= best_eff - 0.02) { best_eff = eff > best_eff ? eff : best_eff; best_t = t; }
     }
     c->threads = env_int("ME_THREADS", best_t);
     if (c->threads % 32 || c->threads < 32 || c->threads > c->kc.maxt)
