@@ -75,23 +75,39 @@ int make_tensor_map(CUtensorMap *tm, const uint8_t *base, int W, int H, int n_fr
 }
 
 struct KernelChoice {
-    const void *fn;
-    int ndy, nq, maxt;
+    const void *fn = nullptr;
+    int ndy = 0, nq = 0, maxt = 0, pitch = 0, rank_bits = 0;
 };
 
-template <int B, int NDY, int NQ, bool K64, int MAXT, int MINB>
+constexpr int kNDY = 5, kNQ = 4, kMaxThreads = 256;
+constexpr int kPitches[3] = {144, 208, 240};   // window row pitches built: odd multiples of 16 (bank-conflict free with NDY = 5)
+
+template <int B, int PITCH, bool K64, int RB>
 KernelChoice choice()
 {
-    return KernelChoice{(const void *)&me::sad_search_kernel<B, NDY, NQ, K64, MAXT, MINB>, NDY, NQ, MAXT};
+    KernelChoice k;
+    k.fn = (const void *)&me::sad_search_kernel<B, kNDY, kNQ, PITCH, K64, RB, kMaxThreads, 2>;
+    k.ndy = kNDY; k.nq = kNQ; k.maxt = kMaxThreads; k.pitch = PITCH; k.rank_bits = RB;
+    return k;
 }
 
-// The patch shapes per block size (see DESIGN.md "inner loop").
-KernelChoice pick_kernel(int B, bool k64)
+template <int PITCH>
+KernelChoice pick_pitch(int B, bool k64)
 {
     switch (B) {
-    case 8:  return k64 ? choice<8, 5, 8, true, 512, 1>() : choice<8, 5, 8, false, 512, 1>();
-    case 16: return k64 ? choice<16, 5, 4, true, 512, 1>() : choice<16, 5, 4, false, 512, 1>();
-    default: return k64 ? choice<32, 5, 4, true, 512, 1>() : choice<32, 5, 4, false, 512, 1>();
+    case 8:  return choice<8, PITCH, false, 16>();      // sad < 2^14, rank < 2^16
+    case 16: return choice<16, PITCH, false, 16>();     // sad < 2^16, rank < 2^16
+    default: return k64 ? choice<32, PITCH, true, 32>() : choice<32, PITCH, false, 14>();   // sad < 2^18
+    }
+}
+
+// One instantiation per (block size, window pitch, key width); see DESIGN.md "inner loop".
+KernelChoice pick_kernel(int B, int pitch, bool k64)
+{
+    switch (pitch) {
+    case 144: return pick_pitch<144>(B, k64);
+    case 208: return pick_pitch<208>(B, k64);
+    default:  return pick_pitch<240>(B, k64);
     }
 }
 
@@ -134,7 +150,7 @@ struct me_ctx {
     me::SearchArgs args{};
     CUtensorMap tm_win{}, tm_ref{};
     KernelChoice kc{};
-    int threads = 0, smem = 0, sm_count = 0;
+    int threads = 0, smem = 0, sm_count = 0, win_pitch = 0;
     int64_t launches = 0;
     int64_t cand_px = 0, cand_px_valid = 0;
 };
@@ -145,28 +161,38 @@ namespace {
 int configure(me_ctx *c)
 {
     const int B = c->p.block, R = c->p.range, U = 2 * R + 1, W = c->W, H = c->H;
+    const int MB = B < 16 ? 16 : B, NSUB = MB / B, NDY = kNDY, NQ = kNQ;
     me::SearchArgs &a = c->args;
     a.W = W; a.H = H; a.R = R; a.U = U;
     a.nbx = W / B; a.nby = H / B; a.nb = a.nbx * a.nby;
+    a.nmbx = ceil_div(a.nbx, NSUB);
     a.frame_pitch = (int)c->pitch;
     a.frame_stride = (long long)c->frame_stride;
     a.min_range = c->p.min_range; a.min_curv = c->p.min_curv; a.subpixel = c->p.subpixel; a.min_valid = c->p.min_valid;
 
-    int rb = 0;
-    while ((1ll << rb) < (long long)U * U) ++rb;
-    a.rank_bits = rb;
-    const long long sad_max = (long long)B * B * 255;
-    const bool k64 = ((sad_max + 1) << rb) > (1ll << 32);
-    c->kc = pick_kernel(B, k64);
-    const int NDY = c->kc.ndy, NQ = c->kc.nq;
+    // key width: (sad << RB) | rank must fit; 32-bit keys use RB = 16 (B <= 16) or 14 (B = 32)
+    if (U > 255) return fail(ME_EUNSUPPORTED, "range %d: the candidate rank needs more than 16 bits", R);
+    const bool k64 = B == 32 && (long long)U * U > (1ll << 14);
 
+    // candidate tiling: dy groups of NDY rows; per shift s the columns q = 0..nq-1 in NQ-wide groups plus leftovers
     a.ndyg = ceil_div(U, NDY);
-    a.cg_start[0] = 0;
+    a.magic_ndyg = a.ndyg <= 1 ? 0u : (unsigned)(0x100000000ull / (unsigned)a.ndyg + 1ull);
+    int ng = 0;
+    a.n_wide = a.n_narrow = 0;
     for (int s = 0; s < 4; ++s) {
         const int nq = (2 * R - s) >= 0 ? (2 * R - s) / 4 + 1 : 0;
-        a.cg_start[s + 1] = a.cg_start[s] + ceil_div(nq, NQ);
+        for (int g = 0; g < nq / NQ; ++g, ++ng, ++a.n_wide) {
+            if (ng >= me::kMaxGroups) return fail(ME_EUNSUPPORTED, "range %d needs more than %d column groups", R, me::kMaxGroups);
+            a.group[ng] = (unsigned short)((s << 12) | (g * NQ));
+        }
     }
-    a.per_j = a.ndyg * a.cg_start[4];
+    for (int s = 0; s < 4; ++s) {
+        const int nq = (2 * R - s) >= 0 ? (2 * R - s) / 4 + 1 : 0;
+        for (int q = (nq / NQ) * NQ; q < nq; ++q, ++ng, ++a.n_narrow) {
+            if (ng >= me::kMaxGroups) return fail(ME_EUNSUPPORTED, "range %d needs more than %d column groups", R, me::kMaxGroups);
+            a.group[ng] = (unsigned short)((s << 12) | q);
+        }
+    }
 
     // Rows: every dy group reads B + NDY - 1 window rows starting at dyg*NDY.
     const int win_rows = a.ndyg * NDY + B - 1;
@@ -174,58 +200,56 @@ int configure(me_ctx *c)
     a.box_rows = ceil_div(win_rows, a.n_row_boxes);
     const int alloc_rows = a.n_row_boxes * a.box_rows;
 
-    // Tile width: the widest tile whose window still fits one TMA box (<= 256 B) and leaves room for
-    // >= 2 CTAs per SM; narrower when the frame is too small to fill the GPU otherwise.
     // TMA needs a 16-byte aligned x origin; tiles start at multiples of 16, so the slack is fixed.
     a.x_off = (16 - R % 16) % 16;
     a.n_bufs = a.x_off ? 5 : 4;
+
+    // Tile width and window pitch.  The pitch is a template constant (every shared load becomes
+    // base + immediate) from a short list of odd multiples of 16 bytes: with NDY = 5 the 8 lanes of a
+    // quarter-warp, which read rows NDY apart, then land in 8 different 16-byte bank groups (r01 ncu:
+    // a 256-byte pitch cost 5.4 wavefronts per LDS.128 and made the kernel shared-memory bound).
+    // Preference: fits the shared-memory cap (>= 3 CTAs per SM), then the widest tile.
     const int smem_cap = env_int("ME_SMEM_CAP", 72 * 1024);
-    int best_tbx = 0;
-    const int forced = env_int("ME_TBX", 0);
-    // Shared-memory banks: the 8 lanes of a quarter-warp read 16 bytes each from rows NDY apart, so the
-    // row pitch in 16-byte units times NDY must be odd for them to land in 8 different bank groups
-    // (r01 ncu: a 256-byte pitch cost 5.4 wavefronts per LDS.128 and made the kernel smem-bound).
-    // Pass 0 accepts only such pitches, pass 1 anything that fits.
-    for (int pass = 0; pass < 2 && !best_tbx; ++pass)
-    for (int tbx = me::kMaxTbx; tbx >= 1; --tbx) {
-        if ((tbx * B) % 16) continue;
-        if (forced && tbx != forced) continue;
-        const int need = a.x_off + tbx * B + 2 * R;
-        int pitch = round_up(need, 16);
-        if ((NDY & 1) && ((pitch / 16) & 1) == 0 && pitch + 16 <= 256) pitch += 16;
-        if (pitch > 256) continue;
-        const bool conflict_free = ((NDY * (pitch / 16)) & 1) != 0;
-        if (pass == 0 && !conflict_free && !forced) continue;
+    const int forced_tmb = env_int("ME_TBX", 0), forced_pitch = env_int("ME_PITCH", 0);
+    int best_tmb = 0, best_pitch = 0, best_smem = 0;
+    bool best_under_cap = false;
+    for (int pi = 0; pi < 3; ++pi) {
+        const int pitch = kPitches[pi];
+        if (forced_pitch && pitch != forced_pitch) continue;
+        int tmb = (pitch - a.x_off - 2 * R) / MB;
+        if (tmb > 256 / MB) tmb = 256 / MB;                       // reference strip is 256 bytes wide
+        if (tmb * NSUB > me::kMaxKeys) tmb = me::kMaxKeys / NSUB;
+        if (tmb > a.nmbx) tmb = a.nmbx;
+        if (forced_tmb) { if (forced_tmb > tmb) continue; tmb = forced_tmb; }
+        if (tmb < 1) continue;
         const int copy = round_up(alloc_rows * pitch, 128);
-        const int smem = a.n_bufs * copy + 256 + round_up(tbx * B * B, 128) + me::kMaxTbx * 8 + 64;
+        const int smem = a.n_bufs * copy + 256 + me::kRefPitch * B + me::kMaxKeys * 8 + 64;
         if (smem > 227 * 1024) continue;
-        const long long tiles = (long long)ceil_div(a.nbx, tbx) * a.nby;
-        if (!forced) {
-            if (smem > smem_cap && tbx > 1) continue;
-            if (tbx > 1 && tiles * (c->max_pairs > 4 ? 4 : c->max_pairs) < 2ll * c->sm_count && tbx * B > 16) continue;
-        }
-        best_tbx = tbx;
-        a.tbx = tbx; a.win_pitch = pitch; a.copy_bytes = copy; a.ref_pitch = tbx * B;
-        c->smem = smem;
-        break;
+        // small frames: keep at least ~2 CTAs per SM in flight for a 4-pair batch
+        if (!forced_tmb)
+            while (tmb > 1 && (long long)ceil_div(a.nmbx, tmb) * a.nby * (c->max_pairs > 4 ? 4 : c->max_pairs) < 2ll * c->sm_count) --tmb;
+        const bool under = smem <= smem_cap;
+        bool better;
+        if (!best_tmb) better = true;
+        else if (under != best_under_cap) better = under;
+        else if (under) better = tmb > best_tmb || (tmb == best_tmb && smem < best_smem);
+        else better = smem < best_smem;
+        if (better) { best_tmb = tmb; best_pitch = pitch; best_smem = smem; best_under_cap = under; a.copy_bytes = copy; }
     }
-    if (!best_tbx)
-        return fail(ME_EUNSUPPORTED, "block %d with range %d needs a %d-byte window row; one TMA box holds 256 "
-                    "(range <= %d for this block size)", B, R, a.x_off + B + 2 * R, (256 - B) / 2);
-    a.tiles_x = ceil_div(a.nbx, a.tbx);
+    if (!best_tmb)
+        return fail(ME_EUNSUPPORTED, "block %d with range %d: the %d-byte window row (or its %d-row copies) does not fit one "
+                    "TMA box / 227 KB of shared memory", B, R, a.x_off + MB + 2 * R, alloc_rows);
+    a.tmb = best_tmb;
+    c->win_pitch = best_pitch;
+    c->smem = best_smem;
+    c->kc = pick_kernel(B, best_pitch, k64);
+    a.tiles_x = ceil_div(a.nmbx, a.tmb);
     a.tiles_per_pair = a.tiles_x * a.nby;
 
     // Threads: whole multiples of 4 warps so that every scheduler of the SM gets the same number of warps
-    // (r01 sweep: 224 threads = 7 warps ran 13 % slower than 128 or 256), then fewest idle lanes.
-    const int total = a.tbx * a.per_j;
-    int best_t = 128;
-    double best_eff = -1;
-    const int tmax = env_int("ME_THREADS_MAX", 256);
-    for (int t = 128; t <= tmax && t <= c->kc.maxt; t += 128) {
-        const double eff = (double)total / ((double)ceil_div(total, t) * t);
-        if (eff >= best_eff - 0.02) { best_eff = eff > best_eff ? eff : best_eff; best_t = t; }
-    }
-    c->threads = env_int("ME_THREADS", best_t);
+    // (r01 sweep: 224 threads = 7 warps ran 13 % slower than 128 or 256).
+    const int total = a.tmb * a.ndyg * a.n_wide;
+    c->threads = env_int("ME_THREADS", total >= 1024 ? 256 : 128);
     if (c->threads % 32 || c->threads < 32 || c->threads > c->kc.maxt)
         return fail(ME_EINVAL, "ME_THREADS=%d is not a multiple of 32 in [32,%d]", c->threads, c->kc.maxt);
     a.use_tma = env_int("ME_NO_TMA", 0) ? 0 : 1;
@@ -415,8 +439,8 @@ int me_create(int device, int height, int width, const me_params *params, int ma
     CREATE_TRY(cudaMemset(c->args.pair_ticket, 0, sizeof(unsigned) * (size_t)max_pairs));
     CREATE_TRY(cudaFuncSetAttribute(c->kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, c->smem));
 #undef CREATE_TRY
-    rc = make_tensor_map(&c->tm_win, c->d_frames, c->W, c->H, max_frames, c->pitch, c->args.win_pitch, c->args.box_rows);
-    if (!rc) rc = make_tensor_map(&c->tm_ref, c->d_frames, c->W, c->H, max_frames, c->pitch, c->args.ref_pitch, B);
+    rc = make_tensor_map(&c->tm_win, c->d_frames, c->W, c->H, max_frames, c->pitch, c->win_pitch, c->args.box_rows);
+    if (!rc) rc = make_tensor_map(&c->tm_ref, c->d_frames, c->W, c->H, max_frames, c->pitch, me::kRefPitch, B);
     if (rc) { me_destroy(c); return rc; }
     *out = c;
     return ME_OK;
@@ -456,7 +480,7 @@ int me_get_geometry(const me_ctx *c, me_geometry *g)
     g->height = c->H; g->width = c->W;
     g->nbx = c->args.nbx; g->nby = c->args.nby;
     g->max_frames = c->max_frames; g->max_pairs = c->max_pairs;
-    g->tile_blocks_x = c->args.tbx; g->threads_per_cta = c->threads; g->smem_bytes = c->smem;
+    g->tile_blocks_x = c->args.tmb * ((c->p.block < 16 ? 16 : c->p.block) / c->p.block); g->threads_per_cta = c->threads; g->smem_bytes = c->smem;
     g->tiles_per_pair = c->args.tiles_per_pair;
     g->cand_px_per_pair = c->cand_px; g->cand_px_per_pair_valid = c->cand_px_valid;
     g->sm_count = c->sm_count; g->uses_tma = c->args.use_tma;
@@ -512,8 +536,8 @@ int me_search_device(me_ctx *c, const uint8_t *d_frames, size_t pitch, int n_fra
     CU_TRY(cudaSetDevice(c->device));
     cudaStream_t st = stream ? (cudaStream_t)stream : c->s_compute;
     CUtensorMap tw, tr;
-    rc = make_tensor_map(&tw, d_frames, c->W, c->H, n_frames, pitch, c->args.win_pitch, c->args.box_rows);
-    if (!rc) rc = make_tensor_map(&tr, d_frames, c->W, c->H, n_frames, pitch, c->args.ref_pitch, c->p.block);
+    rc = make_tensor_map(&tw, d_frames, c->W, c->H, n_frames, pitch, c->win_pitch, c->args.box_rows);
+    if (!rc) rc = make_tensor_map(&tr, d_frames, c->W, c->H, n_frames, pitch, me::kRefPitch, c->p.block);
     if (rc) return rc;
     if (c->have_search) CU_TRY(cudaEventSynchronize(c->ev_search));
     memcpy(c->h_pairs, pairs, sizeof(int32_t) * 2 * (size_t)n_pairs);
@@ -755,8 +779,8 @@ extern "C" int me_search_static_scratch(const uint8_t *d_frames, size_t pitch, i
     unsigned char *base = g_static_dev[dev].scratch;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     CUtensorMap tw, tr;
-    rc = make_tensor_map(&tw, d_frames, width, height, n_frames, pitch, plan.args.win_pitch, plan.args.box_rows);
-    if (!rc) rc = make_tensor_map(&tr, d_frames, width, height, n_frames, pitch, plan.args.ref_pitch, B);
+    rc = make_tensor_map(&tw, d_frames, width, height, n_frames, pitch, plan.win_pitch, plan.args.box_rows);
+    if (!rc) rc = make_tensor_map(&tr, d_frames, width, height, n_frames, pitch, me::kRefPitch, B);
     if (rc) return rc;
     CU_TRY(cudaFuncSetAttribute(plan.kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, plan.smem));
 

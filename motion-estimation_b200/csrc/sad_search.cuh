@@ -1,7 +1,9 @@
 // sad_search.cuh -- device side of the displacement search (sm_100a only).
 //
-// One CTA = one tile = `tbx` horizontally adjacent BxB blocks of the previous frame and the
-// (tbx*B + 2R) x (B + 2R) search window around them in the current frame.
+// One CTA = one tile = `tmb` horizontally adjacent macro-blocks of one block row of the previous
+// frame and the (x_off + tmb*MB + 2R) x (B + 2R) search window around them in the current frame.
+// A macro-block is the 16- or 32-pixel-wide column unit a thread patch works on: one 16x16 or
+// 32x32 block, or two adjacent 8x8 blocks (which then share every loaded word).
 //
 //   staging   One TMA box brings the window into shared memory (x origin rounded down to 16 bytes:
 //             on this hardware a tiled TMA load faults unless its innermost coordinate is 16-byte
@@ -14,7 +16,9 @@
 //   inner     Each thread owns an NDY x NQ patch of candidates (same s, consecutive q, consecutive
 //             dy) and walks the window rows once; a current-frame word loaded into a register is
 //             used for up to NDY*min(NQ,BW) VABSDIFF4.U8.ACC ops, a reference word for NDY*NQ.
-//   argmin    key = (sad << rank_bits) | rank, rank = (dy+R)*(2R+1) + (dx+R): the minimum key is the
+//             The window pitch is a template constant, so every shared load is base + immediate.
+//             Columns that do not fill an NQ-wide patch run as NDY x 1 patches afterwards.
+//   argmin    key = (sad << RB) | rank, rank = (dy+R)*(2R+1) + (dx+R): the minimum key is the
 //             first minimum in raster order whatever the reduction order (spec tie-break).
 //   finalize  one warp per block recomputes the four neighbour SADs from global memory, applies
 //             the parabola fit and the gates and writes the per-block record.
@@ -30,8 +34,18 @@
 
 namespace me {
 
-constexpr int kMaxTbx = 16;
+constexpr int kMaxKeys = 32;          // blocks per tile
+constexpr int kMaxGroups = 96;        // column groups per block (wide + narrow)
+constexpr int kRefPitch = 256;        // bytes per row of the reference strip in shared memory
 constexpr unsigned kFull = 0xffffffffu;
+
+// Compile-time geometry of a block size.
+template <int B> struct Geo {
+    static constexpr int MB = B < 16 ? 16 : B;      // macro-block width in pixels
+    static constexpr int NSUB = MB / B;             // blocks per macro-block
+    static constexpr int BW = MB / 4;               // words per macro-block row
+    static constexpr int SW = B / 4;                // words per block row
+};
 
 struct SearchArgs {
     // frames in device memory: (slots, H, pitch) uint8
@@ -43,20 +57,20 @@ struct SearchArgs {
     // block grid
     int nbx, nby, nb;
     int R, U;                   // U = 2R + 1
-    int tbx, tiles_x, tiles_per_pair;
-    // shared-memory window: 4 shifted copies, each alloc_rows x win_pitch bytes
-    int win_pitch, copy_bytes;
+    int tmb, tiles_x, tiles_per_pair;   // macro-blocks per tile
+    int nmbx;                   // macro-blocks per frame row = ceil(nbx / NSUB)
+    // shared-memory window: 4 shifted copies, each alloc_rows x PITCH bytes
+    int copy_bytes;
     int box_rows, n_row_boxes;
     int x_off;                  // (X0 - R) - (16-byte aligned TMA x origin), 0..15
     int n_bufs;                 // 4 when x_off == 0 (TMA lands in copy 0), else 5 (raw + 4 copies)
-    int ref_pitch;              // tbx * B bytes
-    // candidate tiling
+    // candidate tiling: column groups [0, n_wide) are NQ wide, [n_wide, n_wide + n_narrow) one column
     int ndyg;                   // ceil(U / NDY)
-    int cg_start[5];            // column groups of shift s are [cg_start[s], cg_start[s+1])
-    int per_j;                  // ndyg * cg_start[4] work items per block
+    int n_wide, n_narrow;
+    unsigned short group[kMaxGroups];   // (s << 12) | q0
+    unsigned magic_ndyg;        // fastdiv_magic(ndyg)
     // gates
     int min_range, min_curv, subpixel, min_valid;
-    int rank_bits;
     int use_tma;
     // outputs
     int16_t *blk_mv;            // [P][nb][2]
@@ -104,6 +118,10 @@ __device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *tm, in
                  ::"r"(smem_u32(dst)), "l"(tm), "r"(x), "r"(y), "r"(z), "r"(smem_u32(bar)) : "memory");
 }
 
+// n / d for n*d < 2^32 by one multiply-high (FMA pipe, not the ALU the SAD op needs); magic 0 means d == 1.
+__device__ __forceinline__ unsigned fastdiv_magic(unsigned d) { return d <= 1 ? 0u : (unsigned)(0x100000000ull / d + 1ull); }
+__device__ __forceinline__ int fastdiv(int n, unsigned magic) { return magic ? (int)__umulhi((unsigned)n, magic) : n; }
+
 template <bool K64> struct KeyOf { using T = unsigned int; };
 template <> struct KeyOf<true> { using T = unsigned long long; };
 
@@ -119,50 +137,39 @@ __device__ __forceinline__ unsigned long long warp_min_key(unsigned long long v)
 }
 
 // ---------------------------------------------------------------- inner loop
-// acc[d][q] += SAD over the BxB block for dy = dyg*NDY + d, q = qg*NQ + q (fixed shift s).
-//   cur : word pointer to copy s, row dyg*NDY, word j*BW + qg*NQ
-//   ref : word pointer to the reference tile, row 0, word j*BW
-template <int B, int NDY, int NQ>
-__device__ __forceinline__ void sad_patch(const uint32_t *__restrict__ cur, int cur_pitch_w,
-                                          const uint32_t *__restrict__ ref, int ref_pitch_w,
-                                          uint32_t (&acc)[NDY][NQ])
+// acc[sub][d][q] += SAD of block `sub` of the macro-block for dy index dyi0 + d, column q0 + q.
+//   cur : word pointer to copy s, window row dyi0, word j*BW + q0
+//   ref : word pointer to the reference strip, row 0, word j*BW
+// LW = words per shared load of the current-frame row (4 needs j*BW + q0 to be a multiple of 4).
+template <int B, int NDY, int NQP, int PITCH, int LW>
+__device__ __forceinline__ void sad_patch(const uint32_t *__restrict__ cur, const uint32_t *__restrict__ ref,
+                                          uint32_t (&acc)[Geo<B>::NSUB][NDY][NQP])
 {
-    constexpr int BW = B / 4;                       // words per block row
-    constexpr int NCW = NQ + BW - 1;                // current-frame words needed per window row
-    constexpr int LW = (BW % 4 == 0 && NQ % 4 == 0) ? 4 : ((BW % 2 == 0 && NQ % 2 == 0) ? 2 : 1);
+    constexpr int BW = Geo<B>::BW, SW = Geo<B>::SW;
+    constexpr int PW = PITCH / 4, RPW = kRefPitch / 4;
+    constexpr int NCW = NQP + BW - 1;               // current-frame words needed per window row
     constexpr int NLD = (NCW + LW - 1) / LW;
     uint32_t refw[NDY][BW];                         // rotating window of the last NDY reference rows
 #pragma unroll
     for (int yy = 0; yy < B + NDY - 1; ++yy) {
         uint32_t cw[NLD * LW];
-        const uint32_t *crow = cur + yy * cur_pitch_w;
+        const uint32_t *crow = cur + yy * PW;
 #pragma unroll
         for (int l = 0; l < NLD; ++l) {
             if constexpr (LW == 4) {
-                uint4 v = *reinterpret_cast<const uint4 *>(crow + 4 * l);
+                const uint4 v = *reinterpret_cast<const uint4 *>(crow + 4 * l);
                 cw[4 * l] = v.x; cw[4 * l + 1] = v.y; cw[4 * l + 2] = v.z; cw[4 * l + 3] = v.w;
-            } else if constexpr (LW == 2) {
-                uint2 v = *reinterpret_cast<const uint2 *>(crow + 2 * l);
-                cw[2 * l] = v.x; cw[2 * l + 1] = v.y;
             } else {
                 cw[l] = crow[l];
             }
         }
         if (yy < B) {
-            const uint32_t *rrow = ref + yy * ref_pitch_w;
-            if constexpr (BW % 4 == 0) {
+            const uint32_t *rrow = ref + yy * RPW;
 #pragma unroll
-                for (int l = 0; l < BW / 4; ++l) {
-                    uint4 v = *reinterpret_cast<const uint4 *>(rrow + 4 * l);
-                    refw[yy % NDY][4 * l] = v.x; refw[yy % NDY][4 * l + 1] = v.y;
-                    refw[yy % NDY][4 * l + 2] = v.z; refw[yy % NDY][4 * l + 3] = v.w;
-                }
-            } else {
-#pragma unroll
-                for (int l = 0; l < BW / 2; ++l) {
-                    uint2 v = *reinterpret_cast<const uint2 *>(rrow + 2 * l);
-                    refw[yy % NDY][2 * l] = v.x; refw[yy % NDY][2 * l + 1] = v.y;
-                }
+            for (int l = 0; l < BW / 4; ++l) {
+                const uint4 v = *reinterpret_cast<const uint4 *>(rrow + 4 * l);
+                refw[yy % NDY][4 * l] = v.x; refw[yy % NDY][4 * l + 1] = v.y;
+                refw[yy % NDY][4 * l + 2] = v.z; refw[yy % NDY][4 * l + 3] = v.w;
             }
         }
 #pragma unroll
@@ -172,8 +179,8 @@ __device__ __forceinline__ void sad_patch(const uint32_t *__restrict__ cur, int 
 #pragma unroll
                 for (int w = 0; w < BW; ++w)
 #pragma unroll
-                    for (int q = 0; q < NQ; ++q)
-                        acc[d][q] = vsad4(refw[i % NDY][w], cw[q + w], acc[d][q]);
+                    for (int q = 0; q < NQP; ++q)
+                        acc[w / SW][d][q] = vsad4(refw[i % NDY][w], cw[q + w], acc[w / SW][d][q]);
             }
         }
     }
@@ -215,7 +222,7 @@ __device__ __forceinline__ void finalize_block(const SearchArgs &a, int pair, co
                                                const uint8_t *curf, int bx, int by, uint32_t sad, uint32_t rank,
                                                int lane)
 {
-    constexpr int BW = B / 4;
+    constexpr int SW = B / 4;
     const int R = a.R, U = a.U, x0 = bx * B, y0 = by * B;
     const int dyi = (int)(rank / (uint32_t)U), ui = (int)rank - dyi * U;
     const int dx = ui - R, dy = dyi - R;
@@ -225,8 +232,8 @@ __device__ __forceinline__ void finalize_block(const SearchArgs &a, int pair, co
     const bool yin = dy - 1 >= dylo && dy + 1 <= dyhi;
     const size_t pitch = (size_t)a.frame_pitch;
     uint32_t sxm = 0, sxp = 0, sym = 0, syp = 0, vmn = 0xffffffffu, vmx = 0u;
-    for (int idx = lane; idx < B * BW; idx += 32) {
-        const int row = idx / BW, wd = idx - row * BW;
+    for (int idx = lane; idx < B * SW; idx += 32) {
+        const int row = idx / SW, wd = idx - row * SW;
         const uint32_t rw = __ldg(reinterpret_cast<const uint32_t *>(prevf + (size_t)(y0 + row) * pitch + x0) + wd);
         vmn = __vminu4(vmn, rw);
         vmx = __vmaxu4(vmx, rw);
@@ -382,15 +389,92 @@ __device__ void reduce_pair(const SearchArgs &a, int pair, unsigned *scratch)
     }
 }
 
+// ---------------------------------------------------------------- one work item -> block keys
+// Runs one NDY x NQP candidate patch of macro-block j and folds its best candidate(s) into s_key.
+template <int B, int NDY, int NQP, int PITCH, int LW, bool K64, int RB>
+__device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j, int dyg, int s, int q0,
+                                         const uint8_t *s_win, const uint8_t *s_ref,
+                                         typename KeyOf<K64>::T *s_key, bool tile_interior, int dyi_lo, int dyi_hi,
+                                         int X0, int lane)
+{
+    using KeyT = typename KeyOf<K64>::T;
+    using G = Geo<B>;
+    constexpr KeyT kNone = ~KeyT(0);
+    constexpr int IB = (NDY * NQP <= 2) ? 1 : (NDY * NQP <= 4) ? 2 : (NDY * NQP <= 8) ? 3 : (NDY * NQP <= 16) ? 4
+                     : (NDY * NQP <= 32) ? 5 : 6;                       // bits of the in-patch candidate index
+    static_assert(NDY * NQP <= 64, "patch too large for the packed local key");
+    KeyT best[G::NSUB];
+#pragma unroll
+    for (int sb = 0; sb < G::NSUB; ++sb) best[sb] = kNone;
+    if (active) {
+        uint32_t acc[G::NSUB][NDY][NQP];
+#pragma unroll
+        for (int sb = 0; sb < G::NSUB; ++sb)
+#pragma unroll
+            for (int d = 0; d < NDY; ++d)
+#pragma unroll
+                for (int q = 0; q < NQP; ++q) acc[sb][d][q] = 0;
+        const uint32_t *cur = reinterpret_cast<const uint32_t *>(s_win + (size_t)s * a.copy_bytes) +
+                              dyg * NDY * (PITCH / 4) + j * G::BW + q0;
+        const uint32_t *ref = reinterpret_cast<const uint32_t *>(s_ref) + j * G::BW;
+        sad_patch<B, NDY, NQP, PITCH, LW>(cur, ref, acc);
+
+        const int dyi0 = dyg * NDY, u0 = 4 * q0 + s, twoR = 2 * a.R;
+#pragma unroll
+        for (int sb = 0; sb < G::NSUB; ++sb) {
+            // domain of this block in index space (u = dx + R, dyi = dy + R)
+            const int x0 = X0 + j * G::MB + sb * B;
+            int u_lo = 0, u_hi = twoR;
+            if (!tile_interior) { u_lo = max(0, a.R - x0); u_hi = min(twoR, a.R + a.W - B - x0); }
+            const bool whole = dyi0 >= dyi_lo && dyi0 + NDY - 1 <= dyi_hi && u0 >= u_lo && u0 + 4 * (NQP - 1) <= u_hi;
+            uint32_t lk = 0xffffffffu;                                  // (sad << IB) | index in patch, d-major
+            if (whole) {
+#pragma unroll
+                for (int d = 0; d < NDY; ++d)
+#pragma unroll
+                    for (int q = 0; q < NQP; ++q) lk = min(lk, (acc[sb][d][q] << IB) + (uint32_t)(d * NQP + q));
+            } else {
+#pragma unroll
+                for (int d = 0; d < NDY; ++d)
+#pragma unroll
+                    for (int q = 0; q < NQP; ++q) {
+                        const int dyi = dyi0 + d, u = u0 + 4 * q;
+                        const bool ok = dyi >= dyi_lo && dyi <= dyi_hi && u >= u_lo && u <= u_hi;
+                        const uint32_t v = (acc[sb][d][q] << IB) + (uint32_t)(d * NQP + q);
+                        if (ok) lk = min(lk, v);
+                    }
+            }
+            if (lk != 0xffffffffu) {
+                const int idx = (int)(lk & ((1u << IB) - 1)), d = idx / NQP, q = idx - d * NQP;
+                const uint32_t rank = (uint32_t)((dyi0 + d) * a.U + u0 + 4 * q);
+                best[sb] = ((KeyT)(lk >> IB) << RB) | (KeyT)rank;
+            }
+        }
+    }
+    // block-level argmin: one shared atomic per warp when the warp sits in one macro-block
+    const int j0 = __shfl_sync(kFull, j, 0);
+    const bool uniform = __all_sync(kFull, j == j0);
+#pragma unroll
+    for (int sb = 0; sb < G::NSUB; ++sb) {
+        if (uniform) {
+            const KeyT m = warp_min_key(best[sb]);
+            if (lane == 0 && m != kNone) atomicMin(&s_key[j0 * G::NSUB + sb], m);
+        } else if (best[sb] != kNone) {
+            atomicMin(&s_key[j * G::NSUB + sb], best[sb]);
+        }
+    }
+}
+
 // ---------------------------------------------------------------- the search kernel
-template <int B, int NDY, int NQ, bool K64, int MAXT, int MINB>
+template <int B, int NDY, int NQ, int PITCH, bool K64, int RB, int MAXT, int MINB>
 __global__ void __launch_bounds__(MAXT, MINB)
 sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_constant__ CUtensorMap tm_ref,
                   const SearchArgs a)
 {
     using KeyT = typename KeyOf<K64>::T;
-    constexpr int BW = B / 4;
+    using G = Geo<B>;
     constexpr KeyT kNone = ~KeyT(0);
+    constexpr int LWW = (NQ % 4 == 0) ? 4 : 1;       // wide patches start on 16-byte boundaries when NQ % 4 == 0
     extern __shared__ __align__(1024) uint8_t smem[];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
@@ -398,28 +482,29 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     const int tr = blockIdx.x - pair * a.tiles_per_pair;
     const int ty = tr / a.tiles_x, tx = tr - ty * a.tiles_x;
     const int prev_slot = __ldg(a.pairs + 2 * pair), cur_slot = __ldg(a.pairs + 2 * pair + 1);
-    const int X0 = tx * a.tbx * B, Y0 = ty * B;
-    const int nj = min(a.tbx, a.nbx - tx * a.tbx);
+    const int X0 = tx * a.tmb * G::MB, Y0 = ty * B;
+    const int nj = min(a.tmb, a.nmbx - tx * a.tmb);                    // macro-blocks in this tile
+    const int nblk = min(nj * G::NSUB, a.nbx - tx * a.tmb * G::NSUB);  // blocks in this tile
 
     uint8_t *s_win = smem;                                            // 4 shifted copies
     uint8_t *s_raw = a.x_off ? smem + 4 * (size_t)a.copy_bytes : smem; // TMA destination
     uint8_t *s_ref = smem + (size_t)a.n_bufs * a.copy_bytes + 256;    // 256 B of slack for tile over-reads
-    const int ref_bytes = (a.ref_pitch * B + 127) & ~127;
-    KeyT *s_key = reinterpret_cast<KeyT *>(s_ref + ref_bytes);         // [kMaxTbx]
-    uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_ref + ref_bytes + kMaxTbx * 8);
+    constexpr int ref_bytes = kRefPitch * B;
+    KeyT *s_key = reinterpret_cast<KeyT *>(s_ref + ref_bytes);         // [kMaxKeys]
+    uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_ref + ref_bytes + kMaxKeys * 8);
     int *s_last = reinterpret_cast<int *>(s_bar + 1);
 
-    if (tid < kMaxTbx) s_key[tid] = kNone;
+    if (tid < kMaxKeys) s_key[tid] = kNone;
 
     const int wx0 = X0 - a.R - a.x_off;                               // multiple of 16
     if (a.use_tma) {
         if (tid == 0) mbar_init(s_bar, 1);
         __syncthreads();
         if (tid == 0) {
-            const uint32_t bytes = (uint32_t)a.n_row_boxes * a.box_rows * a.win_pitch + (uint32_t)a.ref_pitch * B;
+            const uint32_t bytes = (uint32_t)a.n_row_boxes * a.box_rows * PITCH + (uint32_t)ref_bytes;
             mbar_expect_tx(s_bar, bytes);
             for (int rb = 0; rb < a.n_row_boxes; ++rb)
-                tma_load_3d(s_raw + (size_t)rb * a.box_rows * a.win_pitch, &tm_win, wx0, Y0 - a.R + rb * a.box_rows,
+                tma_load_3d(s_raw + (size_t)rb * a.box_rows * PITCH, &tm_win, wx0, Y0 - a.R + rb * a.box_rows,
                             cur_slot, s_bar);
             tma_load_3d(s_ref, &tm_ref, X0, Y0, prev_slot, s_bar);
         }
@@ -429,15 +514,15 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
         const uint8_t *curf = a.frames + (long long)cur_slot * a.frame_stride;
         const uint8_t *prevf = a.frames + (long long)prev_slot * a.frame_stride;
         const int rows = a.n_row_boxes * a.box_rows;
-        for (int i = tid; i < rows * a.win_pitch; i += blockDim.x) {
-            const int r = i / a.win_pitch, c = i - r * a.win_pitch;
+        for (int i = tid; i < rows * PITCH; i += blockDim.x) {
+            const int r = i / PITCH, c = i - r * PITCH;
             const int gx = wx0 + c, gy = Y0 - a.R + r;
             uint8_t v = 0;
             if (gx >= 0 && gx < a.W && gy >= 0 && gy < a.H) v = curf[(size_t)gy * a.frame_pitch + gx];
             s_raw[i] = v;
         }
-        for (int i = tid; i < a.ref_pitch * B; i += blockDim.x) {
-            const int r = i / a.ref_pitch, c = i - r * a.ref_pitch;
+        for (int i = tid; i < ref_bytes; i += blockDim.x) {
+            const int r = i / kRefPitch, c = i - r * kRefPitch;
             const int gx = X0 + c, gy = Y0 + r;
             s_ref[i] = (gx < a.W && gy < a.H) ? prevf[(size_t)gy * a.frame_pitch + gx] : 0;
         }
@@ -446,93 +531,87 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
 
     // ---- derive the byte-shifted copies: copy s, byte k of a row = raw byte (x_off + s + k)
     {
-        const int chunks = a.n_row_boxes * a.box_rows * (a.win_pitch >> 4);   // 16-byte chunks per copy
+        const int chunks = a.n_row_boxes * a.box_rows * (PITCH >> 4);   // 16-byte chunks per copy
         const uint32_t *raw = reinterpret_cast<const uint32_t *>(s_raw);
-        for (int i = tid; i < chunks; i += blockDim.x) {
-            uint32_t w[9];
-            const uint4 v0 = *reinterpret_cast<const uint4 *>(raw + 4 * i);
-            const uint4 v1 = *reinterpret_cast<const uint4 *>(raw + 4 * i + 4);   // may run into the slack: unused bytes only
-            w[0] = v0.x; w[1] = v0.y; w[2] = v0.z; w[3] = v0.w; w[4] = v1.x; w[5] = v1.y; w[6] = v1.z; w[7] = v1.w;
-            w[8] = raw[4 * i + 8];
+        if (a.x_off == 0) {                                             // copy 0 is the TMA destination itself
+            for (int i = tid; i < chunks; i += blockDim.x) {
+                const uint4 v = *reinterpret_cast<const uint4 *>(raw + 4 * i);
+                const uint32_t w4 = raw[4 * i + 4];                     // next chunk's first word (slack at the very end)
 #pragma unroll
-            for (int s = 0; s < 4; ++s) {
-                if (s == 0 && a.x_off == 0) continue;                 // copy 0 is the TMA destination itself
-                const int sh = a.x_off + s, wo = sh >> 2;
-                const unsigned bits = (unsigned)(sh & 3) * 8;
-                uint4 o;
-                // wo is 0..4 (x_off <= 15, s <= 3): select statically to keep w[] in registers
-                uint32_t e[5];
+                for (int s = 1; s < 4; ++s) {
+                    uint4 o;
+                    o.x = __funnelshift_r(v.x, v.y, 8 * s);
+                    o.y = __funnelshift_r(v.y, v.z, 8 * s);
+                    o.z = __funnelshift_r(v.z, v.w, 8 * s);
+                    o.w = __funnelshift_r(v.w, w4, 8 * s);
+                    *reinterpret_cast<uint4 *>(s_win + (size_t)s * a.copy_bytes + 16 * (size_t)i) = o;
+                }
+            }
+        } else {
+            for (int i = tid; i < chunks; i += blockDim.x) {
+                uint32_t w[9];
+                const uint4 v0 = *reinterpret_cast<const uint4 *>(raw + 4 * i);
+                const uint4 v1 = *reinterpret_cast<const uint4 *>(raw + 4 * i + 4);   // may run into the slack: unused bytes only
+                w[0] = v0.x; w[1] = v0.y; w[2] = v0.z; w[3] = v0.w; w[4] = v1.x; w[5] = v1.y; w[6] = v1.z; w[7] = v1.w;
+                w[8] = raw[4 * i + 8];
 #pragma unroll
-                for (int k = 0; k < 5; ++k)
-                    e[k] = wo == 0 ? w[k] : wo == 1 ? w[k + 1] : wo == 2 ? w[k + 2] : wo == 3 ? w[k + 3] : w[k + 4];
-                o.x = __funnelshift_r(e[0], e[1], bits);
-                o.y = __funnelshift_r(e[1], e[2], bits);
-                o.z = __funnelshift_r(e[2], e[3], bits);
-                o.w = __funnelshift_r(e[3], e[4], bits);
-                *reinterpret_cast<uint4 *>(s_win + (size_t)s * a.copy_bytes + 16 * (size_t)i) = o;
+                for (int s = 0; s < 4; ++s) {
+                    const int sh = a.x_off + s, wo = sh >> 2;
+                    const unsigned bits = (unsigned)(sh & 3) * 8;
+                    uint32_t e[5];                  // wo is 0..4: select statically to keep w[] in registers
+#pragma unroll
+                    for (int k = 0; k < 5; ++k)
+                        e[k] = wo == 0 ? w[k] : wo == 1 ? w[k + 1] : wo == 2 ? w[k + 2] : wo == 3 ? w[k + 3] : w[k + 4];
+                    uint4 o;
+                    o.x = __funnelshift_r(e[0], e[1], bits);
+                    o.y = __funnelshift_r(e[1], e[2], bits);
+                    o.z = __funnelshift_r(e[2], e[3], bits);
+                    o.w = __funnelshift_r(e[3], e[4], bits);
+                    *reinterpret_cast<uint4 *>(s_win + (size_t)s * a.copy_bytes + 16 * (size_t)i) = o;
+                }
             }
         }
         __syncthreads();
     }
 
-    // ---- candidate patches
-    const int total = nj * a.per_j;
-    const int iters = (total + (int)blockDim.x - 1) / (int)blockDim.x;
-    const int cur_pitch_w = a.win_pitch >> 2, ref_pitch_w = a.ref_pitch >> 2;
-    const int dyi_lo = max(0, a.R - Y0), dyi_hi = min(2 * a.R, a.R + a.H - B - Y0);
-    const KeyT scale = KeyT(1) << a.rank_bits;
-    for (int it = 0; it < iters; ++it) {
-        const int w_raw = it * (int)blockDim.x + tid;
-        const bool active = w_raw < total;
-        const int w = active ? w_raw : total - 1;
-        const int j = w / a.per_j, r = w - j * a.per_j;
-        const int cg = r / a.ndyg, dyg = r - cg * a.ndyg;       // dy group varies fastest across lanes
-        const int s = (cg >= a.cg_start[1]) + (cg >= a.cg_start[2]) + (cg >= a.cg_start[3]);
-        const int qg = cg - a.cg_start[s];
-        KeyT best = kNone;
-        if (active) {
-            uint32_t acc[NDY][NQ];
-#pragma unroll
-            for (int d = 0; d < NDY; ++d)
-#pragma unroll
-                for (int q = 0; q < NQ; ++q) acc[d][q] = 0;
-            const uint32_t *cur = reinterpret_cast<const uint32_t *>(s_win + (size_t)s * a.copy_bytes) +
-                                  dyg * NDY * cur_pitch_w + j * BW + qg * NQ;
-            const uint32_t *ref = reinterpret_cast<const uint32_t *>(s_ref) + j * BW;
-            sad_patch<B, NDY, NQ>(cur, cur_pitch_w, ref, ref_pitch_w, acc);
-
-            const int x0 = X0 + j * B;
-            const int u_lo = max(0, a.R - x0), u_hi = min(2 * a.R, a.R + a.W - B - x0);
-            const int dyi0 = dyg * NDY, u0 = 4 * qg * NQ + s;
-            const bool whole = dyi0 >= dyi_lo && dyi0 + NDY - 1 <= dyi_hi && u0 >= u_lo && u0 + 4 * (NQ - 1) <= u_hi;
-            const KeyT rank0 = (KeyT)(dyi0 * a.U + u0);
-            if (whole) {
-#pragma unroll
-                for (int d = 0; d < NDY; ++d)
-#pragma unroll
-                    for (int q = 0; q < NQ; ++q) {
-                        const KeyT key = (KeyT)acc[d][q] * scale + (rank0 + (KeyT)(d * a.U + 4 * q));
-                        best = key < best ? key : best;
-                    }
-            } else {
-#pragma unroll
-                for (int d = 0; d < NDY; ++d)
-#pragma unroll
-                    for (int q = 0; q < NQ; ++q) {
-                        const int dyi = dyi0 + d, u = u0 + 4 * q;
-                        const bool ok = dyi >= dyi_lo && dyi <= dyi_hi && u >= u_lo && u <= u_hi;
-                        const KeyT key = (KeyT)acc[d][q] * scale + (rank0 + (KeyT)(d * a.U + 4 * q));
-                        if (ok && key < best) best = key;
-                    }
-            }
+    // ---- candidate patches.  dy groups that lie wholly outside this block row's domain are not
+    //      enumerated at all (they are most of the work on the 64-pixel-tall example recordings).
+    const int twoR = 2 * a.R;
+    const int dyi_lo = max(0, a.R - Y0), dyi_hi = min(twoR, a.R + a.H - B - Y0);
+    const bool tile_interior = dyi_lo == 0 && dyi_hi == twoR && X0 - a.R >= 0 && X0 + nblk * B + a.R <= a.W;
+    const int dyg_lo = dyi_lo / NDY, dyg_hi = dyi_hi / NDY;
+    const int nd = dyg_hi - dyg_lo + 1;
+    const unsigned magic_nd = nd == a.ndyg ? a.magic_ndyg : fastdiv_magic((unsigned)nd);
+    {   // wide patches: NDY x NQ
+        const int per_j = nd * a.n_wide;
+        const int total = nj * per_j;
+        const unsigned magic_pj = fastdiv_magic((unsigned)per_j);
+        const int iters = (total + (int)blockDim.x - 1) / (int)blockDim.x;
+        for (int it = 0; it < iters; ++it) {
+            const int w_raw = it * (int)blockDim.x + tid;
+            const bool active = w_raw < total;
+            const int w = active ? w_raw : total - 1;
+            const int j = fastdiv(w, magic_pj), r = w - j * per_j;
+            const int cg = fastdiv(r, magic_nd), dyg = dyg_lo + r - cg * nd;   // dy group varies fastest across lanes
+            const unsigned g = a.group[cg];
+            run_item<B, NDY, NQ, PITCH, LWW, K64, RB>(a, active, j, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
+                                                      s_key, tile_interior, dyi_lo, dyi_hi, X0, lane);
         }
-        // block-level argmin: one shared atomic per warp when the warp sits in one block
-        const int j0 = __shfl_sync(kFull, j, 0);
-        if (__all_sync(kFull, j == j0)) {
-            const KeyT m = warp_min_key(best);
-            if (lane == 0 && m != kNone) atomicMin(&s_key[j0], m);
-        } else if (best != kNone) {
-            atomicMin(&s_key[j], best);
+    }
+    if (a.n_narrow > 0) {   // leftover columns: NDY x 1
+        const int per_j = nd * a.n_narrow;
+        const int total = nj * per_j;
+        const unsigned magic_pj = fastdiv_magic((unsigned)per_j);
+        const int iters = (total + (int)blockDim.x - 1) / (int)blockDim.x;
+        for (int it = 0; it < iters; ++it) {
+            const int w_raw = it * (int)blockDim.x + tid;
+            const bool active = w_raw < total;
+            const int w = active ? w_raw : total - 1;
+            const int j = fastdiv(w, magic_pj), r = w - j * per_j;
+            const int cg = fastdiv(r, magic_nd), dyg = dyg_lo + r - cg * nd;
+            const unsigned g = a.group[a.n_wide + cg];
+            run_item<B, NDY, 1, PITCH, 1, K64, RB>(a, active, j, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
+                                                   s_key, tile_interior, dyi_lo, dyi_hi, X0, lane);
         }
     }
     __syncthreads();
@@ -541,10 +620,10 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     {
         const uint8_t *curf = a.frames + (long long)cur_slot * a.frame_stride;
         const uint8_t *prevf = a.frames + (long long)prev_slot * a.frame_stride;
-        const KeyT rmask = scale - 1;
-        for (int j = warp; j < nj; j += nwarps) {
-            const KeyT key = s_key[j];
-            finalize_block<B>(a, pair, prevf, curf, tx * a.tbx + j, ty, (uint32_t)(key >> a.rank_bits),
+        constexpr KeyT rmask = (KeyT(1) << RB) - 1;
+        for (int jb = warp; jb < nblk; jb += nwarps) {
+            const KeyT key = s_key[jb];
+            finalize_block<B>(a, pair, prevf, curf, tx * a.tmb * G::NSUB + jb, ty, (uint32_t)(key >> RB),
                               (uint32_t)(key & rmask), lane);
         }
     }
