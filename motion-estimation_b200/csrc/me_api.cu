@@ -86,7 +86,7 @@ template <int B, int PITCH, bool K64, int RB>
 KernelChoice choice()
 {
     KernelChoice k;
-    k.fn = (const void *)&me::sad_search_kernel<B, kNDY, kNQ, PITCH, K64, RB, kMaxThreads, 2>;
+    k.fn = (const void *)&me::sad_search_kernel<B, kNDY, kNQ, PITCH, K64, RB, kMaxThreads, 3>;
     k.ndy = kNDY; k.nq = kNQ; k.maxt = kMaxThreads; k.pitch = PITCH; k.rank_bits = RB;
     return k;
 }
@@ -438,6 +438,7 @@ int me_create(int device, int height, int width, const me_params *params, int ma
     CREATE_TRY(cudaMalloc(&c->args.pair_ticket, sizeof(unsigned) * (size_t)max_pairs));
     CREATE_TRY(cudaMemset(c->args.pair_ticket, 0, sizeof(unsigned) * (size_t)max_pairs));
     CREATE_TRY(cudaFuncSetAttribute(c->kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, c->smem));
+    CREATE_TRY(cudaFuncSetAttribute(c->kc.fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
 #undef CREATE_TRY
     rc = make_tensor_map(&c->tm_win, c->d_frames, c->W, c->H, max_frames, c->pitch, c->win_pitch, c->args.box_rows);
     if (!rc) rc = make_tensor_map(&c->tm_ref, c->d_frames, c->W, c->H, max_frames, c->pitch, me::kRefPitch, B);
@@ -783,6 +784,7 @@ extern "C" int me_search_static_scratch(const uint8_t *d_frames, size_t pitch, i
     if (!rc) rc = make_tensor_map(&tr, d_frames, width, height, n_frames, pitch, me::kRefPitch, B);
     if (rc) return rc;
     CU_TRY(cudaFuncSetAttribute(plan.kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, plan.smem));
+    CU_TRY(cudaFuncSetAttribute(plan.kc.fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
 
     me::SearchArgs a = plan.args;
     a.frames = d_frames;

@@ -400,9 +400,11 @@ __device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j
     using KeyT = typename KeyOf<K64>::T;
     using G = Geo<B>;
     constexpr KeyT kNone = ~KeyT(0);
-    constexpr int IB = (NDY * NQP <= 2) ? 1 : (NDY * NQP <= 4) ? 2 : (NDY * NQP <= 8) ? 3 : (NDY * NQP <= 16) ? 4
-                     : (NDY * NQP <= 32) ? 5 : 6;                       // bits of the in-patch candidate index
-    static_assert(NDY * NQP <= 64, "patch too large for the packed local key");
+    // Thread-local key = sad * KM + (index in patch): order-preserving for any KM > max index.  KM is
+    // deliberately NOT a power of two: the compiler then emits IMAD (FMA pipe, idle here) instead of
+    // LEA/SHF, which would compete with VABSDIFF4 for the ALU pipe.
+    constexpr uint32_t KM = 37;
+    static_assert(NDY * NQP <= 37, "patch too large for the packed local key");
     KeyT best[G::NSUB];
 #pragma unroll
     for (int sb = 0; sb < G::NSUB; ++sb) best[sb] = kNone;
@@ -426,13 +428,14 @@ __device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j
             const int x0 = X0 + j * G::MB + sb * B;
             int u_lo = 0, u_hi = twoR;
             if (!tile_interior) { u_lo = max(0, a.R - x0); u_hi = min(twoR, a.R + a.W - B - x0); }
-            const bool whole = dyi0 >= dyi_lo && dyi0 + NDY - 1 <= dyi_hi && u0 >= u_lo && u0 + 4 * (NQP - 1) <= u_hi;
-            uint32_t lk = 0xffffffffu;                                  // (sad << IB) | index in patch, d-major
+            const bool whole = tile_interior ? (dyi0 + NDY - 1 <= dyi_hi)
+                                             : (dyi0 >= dyi_lo && dyi0 + NDY - 1 <= dyi_hi && u0 >= u_lo && u0 + 4 * (NQP - 1) <= u_hi);
+            uint32_t lk = 0xffffffffu;                                  // sad * KM + index in patch, d-major
             if (whole) {
 #pragma unroll
                 for (int d = 0; d < NDY; ++d)
 #pragma unroll
-                    for (int q = 0; q < NQP; ++q) lk = min(lk, (acc[sb][d][q] << IB) + (uint32_t)(d * NQP + q));
+                    for (int q = 0; q < NQP; ++q) lk = min(lk, acc[sb][d][q] * KM + (uint32_t)(d * NQP + q));
             } else {
 #pragma unroll
                 for (int d = 0; d < NDY; ++d)
@@ -440,14 +443,15 @@ __device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j
                     for (int q = 0; q < NQP; ++q) {
                         const int dyi = dyi0 + d, u = u0 + 4 * q;
                         const bool ok = dyi >= dyi_lo && dyi <= dyi_hi && u >= u_lo && u <= u_hi;
-                        const uint32_t v = (acc[sb][d][q] << IB) + (uint32_t)(d * NQP + q);
+                        const uint32_t v = acc[sb][d][q] * KM + (uint32_t)(d * NQP + q);
                         if (ok) lk = min(lk, v);
                     }
             }
             if (lk != 0xffffffffu) {
-                const int idx = (int)(lk & ((1u << IB) - 1)), d = idx / NQP, q = idx - d * NQP;
+                const uint32_t sad = lk / KM;
+                const int idx = (int)(lk - sad * KM), d = idx / NQP, q = idx - d * NQP;
                 const uint32_t rank = (uint32_t)((dyi0 + d) * a.U + u0 + 4 * q);
-                best[sb] = ((KeyT)(lk >> IB) << RB) | (KeyT)rank;
+                best[sb] = ((KeyT)sad << RB) | (KeyT)rank;
             }
         }
     }
