@@ -249,7 +249,7 @@ int configure(me_ctx *c)
     // Threads: whole multiples of 4 warps so that every scheduler of the SM gets the same number of warps
     // (r01 sweep: 224 threads = 7 warps ran 13 % slower than 128 or 256).
     const int total = a.tmb * a.ndyg * a.n_wide;
-    c->threads = env_int("ME_THREADS", total >= 1024 ? 256 : 128);
+    c->threads = env_int("ME_THREADS", total >= 512 ? 256 : 128);
     if (c->threads % 32 || c->threads < 32 || c->threads > c->kc.maxt)
         return fail(ME_EINVAL, "ME_THREADS=%d is not a multiple of 32 in [32,%d]", c->threads, c->kc.maxt);
     a.use_tma = env_int("ME_NO_TMA", 0) ? 0 : 1;

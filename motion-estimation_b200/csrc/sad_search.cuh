@@ -422,34 +422,50 @@ __device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j
         sad_patch<B, NDY, NQP, PITCH, LW>(cur, ref, acc);
 
         const int dyi0 = dyg * NDY, u0 = 4 * q0 + s, twoR = 2 * a.R;
+        // domain of each block in index space (u = dx + R, dyi = dy + R)
+        int u_lo[G::NSUB], u_hi[G::NSUB];
+        bool whole = dyi0 >= dyi_lo && dyi0 + NDY - 1 <= dyi_hi;
 #pragma unroll
         for (int sb = 0; sb < G::NSUB; ++sb) {
-            // domain of this block in index space (u = dx + R, dyi = dy + R)
-            const int x0 = X0 + j * G::MB + sb * B;
-            int u_lo = 0, u_hi = twoR;
-            if (!tile_interior) { u_lo = max(0, a.R - x0); u_hi = min(twoR, a.R + a.W - B - x0); }
-            const bool whole = tile_interior ? (dyi0 + NDY - 1 <= dyi_hi)
-                                             : (dyi0 >= dyi_lo && dyi0 + NDY - 1 <= dyi_hi && u0 >= u_lo && u0 + 4 * (NQP - 1) <= u_hi);
-            uint32_t lk = 0xffffffffu;                                  // sad * KM + index in patch, d-major
-            if (whole) {
+            u_lo[sb] = 0; u_hi[sb] = twoR;
+            if (!tile_interior) {
+                const int x0 = X0 + j * G::MB + sb * B;
+                u_lo[sb] = max(0, a.R - x0); u_hi[sb] = min(twoR, a.R + a.W - B - x0);
+                whole = whole && u0 >= u_lo[sb] && u0 + 4 * (NQP - 1) <= u_hi[sb];
+            }
+        }
+        uint32_t lk[G::NSUB];                                           // sad * KM + index in patch, d-major
+        // A real (warp-uniform) branch: left to itself the compiler if-converts the two paths and then
+        // every patch pays the per-candidate domain test on the SAD op's pipe.
+        if (__all_sync(__activemask(), whole)) {
+#pragma unroll
+            for (int sb = 0; sb < G::NSUB; ++sb) {
+                lk[sb] = 0xffffffffu;
 #pragma unroll
                 for (int d = 0; d < NDY; ++d)
 #pragma unroll
-                    for (int q = 0; q < NQP; ++q) lk = min(lk, acc[sb][d][q] * KM + (uint32_t)(d * NQP + q));
-            } else {
+                    for (int q = 0; q < NQP; ++q) lk[sb] = min(lk[sb], acc[sb][d][q] * KM + (uint32_t)(d * NQP + q));
+            }
+        } else {
+#pragma unroll
+            for (int sb = 0; sb < G::NSUB; ++sb) {
+                lk[sb] = 0xffffffffu;
 #pragma unroll
                 for (int d = 0; d < NDY; ++d)
 #pragma unroll
                     for (int q = 0; q < NQP; ++q) {
                         const int dyi = dyi0 + d, u = u0 + 4 * q;
-                        const bool ok = dyi >= dyi_lo && dyi <= dyi_hi && u >= u_lo && u <= u_hi;
+                        const bool ok = dyi >= dyi_lo && dyi <= dyi_hi && u >= u_lo[sb] && u <= u_hi[sb];
                         const uint32_t v = acc[sb][d][q] * KM + (uint32_t)(d * NQP + q);
-                        if (ok) lk = min(lk, v);
+                        if (ok) lk[sb] = min(lk[sb], v);
                     }
             }
-            if (lk != 0xffffffffu) {
-                const uint32_t sad = lk / KM;
-                const int idx = (int)(lk - sad * KM), d = idx / NQP, q = idx - d * NQP;
+        }
+#pragma unroll
+        for (int sb = 0; sb < G::NSUB; ++sb) {
+            if (lk[sb] != 0xffffffffu) {
+                const uint32_t sad = lk[sb] / KM;
+                const int idx = (int)(lk[sb] - sad * KM), d = idx / NQP, q = idx - d * NQP;
                 const uint32_t rank = (uint32_t)((dyi0 + d) * a.U + u0 + 4 * q);
                 best[sb] = ((KeyT)sad << RB) | (KeyT)rank;
             }
