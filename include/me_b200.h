@@ -54,7 +54,7 @@ typedef struct me_ctx me_ctx;
  * estimate_vel_vid.py:308-309); they are the knobs of the block search that replaces it. */
 typedef struct me_params {
     int32_t block;      /* B: 8, 16 or 32                                                     */
-    int32_t range;      /* R: 1 .. (256 - B) / 2   (one TMA box per window; larger R: later)  */
+    int32_t range;      /* R: 1 .. 127 (larger ranges are cut into slabs, one CTA each)       */
     int32_t min_range;  /* texture gate: block max-min >= min_range grey levels               */
     int32_t subpixel;   /* 0 = integer displacements only                                     */
     int32_t min_valid;  /* pair flag = nvalid_x >= max(min_valid, 1)                          */
@@ -85,6 +85,9 @@ typedef struct me_geometry {
     int64_t cand_px_per_pair_valid;   /* in-frame candidates only (algorithmic work)              */
     int32_t sm_count;
     int32_t uses_tma;
+    int32_t slabs_x, slabs_y;   /* the candidate square is cut into slabs_x * slabs_y CTAs per tile   */
+    int32_t window_pitch;       /* bytes per shared-memory window row (a template constant)         */
+    int32_t reserved;
 } me_geometry;
 
 const char *me_last_error(void);          /* thread-local, never NULL                         */

@@ -171,84 +171,114 @@ int configure(me_ctx *c)
     a.min_range = c->p.min_range; a.min_curv = c->p.min_curv; a.subpixel = c->p.subpixel; a.min_valid = c->p.min_valid;
 
     // key width: (sad << RB) | rank must fit; 32-bit keys use RB = 16 (B <= 16) or 14 (B = 32)
-    if (U > 255) return fail(ME_EUNSUPPORTED, "range %d: the candidate rank needs more than 16 bits", R);
+    if (U > 255) return fail(ME_EUNSUPPORTED, "range %d: the candidate rank needs more than 16 bits (range <= 127)", R);
     const bool k64 = B == 32 && (long long)U * U > (1ll << 14);
 
-    // candidate tiling: dy groups of NDY rows; per shift s the columns q = 0..nq-1 in NQ-wide groups plus leftovers
-    a.ndyg = ceil_div(U, NDY);
-    a.magic_ndyg = a.ndyg <= 1 ? 0u : (unsigned)(0x100000000ull / (unsigned)a.ndyg + 1ull);
-    int ng = 0;
-    a.n_wide = a.n_narrow = 0;
-    for (int s = 0; s < 4; ++s) {
-        const int nq = (2 * R - s) >= 0 ? (2 * R - s) / 4 + 1 : 0;
-        for (int g = 0; g < nq / NQ; ++g, ++ng, ++a.n_wide) {
-            if (ng >= me::kMaxGroups) return fail(ME_EUNSUPPORTED, "range %d needs more than %d column groups", R, me::kMaxGroups);
-            a.group[ng] = (unsigned short)((s << 12) | (g * NQ));
-        }
-    }
-    for (int s = 0; s < 4; ++s) {
-        const int nq = (2 * R - s) >= 0 ? (2 * R - s) / 4 + 1 : 0;
-        for (int q = (nq / NQ) * NQ; q < nq; ++q, ++ng, ++a.n_narrow) {
-            if (ng >= me::kMaxGroups) return fail(ME_EUNSUPPORTED, "range %d needs more than %d column groups", R, me::kMaxGroups);
-            a.group[ng] = (unsigned short)((s << 12) | q);
-        }
-    }
-
-    // Rows: every dy group reads B + NDY - 1 window rows starting at dyg*NDY.
-    const int win_rows = a.ndyg * NDY + B - 1;
-    a.n_row_boxes = ceil_div(win_rows, 256);
-    a.box_rows = ceil_div(win_rows, a.n_row_boxes);
-    const int alloc_rows = a.n_row_boxes * a.box_rows;
-
-    // TMA needs a 16-byte aligned x origin; tiles start at multiples of 16, so the slack is fixed.
+    // TMA needs a 16-byte aligned x origin; tiles and slabs start at multiples of 16, so the slack is fixed.
     a.x_off = (16 - R % 16) % 16;
     a.n_bufs = a.x_off ? 5 : 4;
 
-    // Tile width and window pitch.  The pitch is a template constant (every shared load becomes
-    // base + immediate) from a short list of odd multiples of 16 bytes: with NDY = 5 the 8 lanes of a
-    // quarter-warp, which read rows NDY apart, then land in 8 different 16-byte bank groups (r01 ncu:
-    // a 256-byte pitch cost 5.4 wavefronts per LDS.128 and made the kernel shared-memory bound).
-    // Preference: fits the shared-memory cap (>= 3 CTAs per SM), then the widest tile.
+    // Launch plan.  The candidate square is cut into nsx x nsy slabs (one CTA each) until a slab's
+    // window fits the shared-memory cap; within that, the widest tile and the fewest slabs win.  The
+    // window pitch is a template constant (every shared load becomes base + immediate) from a short
+    // list of odd multiples of 16 bytes: with NDY = 5 the 8 lanes of a quarter-warp, which read rows
+    // NDY apart, then land in 8 different 16-byte bank groups (r01 ncu: a 256-byte pitch cost 5.4
+    // wavefronts per LDS.128 and made the kernel shared-memory bound).
     const int smem_cap = env_int("ME_SMEM_CAP", 72 * 1024);
     const int forced_tmb = env_int("ME_TBX", 0), forced_pitch = env_int("ME_PITCH", 0);
-    int best_tmb = 0, best_pitch = 0, best_smem = 0;
-    bool best_under_cap = false;
-    for (int pi = 0; pi < 3; ++pi) {
-        const int pitch = kPitches[pi];
-        if (forced_pitch && pitch != forced_pitch) continue;
-        int tmb = (pitch - a.x_off - 2 * R) / MB;
-        if (tmb > 256 / MB) tmb = 256 / MB;                       // reference strip is 256 bytes wide
-        if (tmb * NSUB > me::kMaxKeys) tmb = me::kMaxKeys / NSUB;
-        if (tmb > a.nmbx) tmb = a.nmbx;
-        if (forced_tmb) { if (forced_tmb > tmb) continue; tmb = forced_tmb; }
-        if (tmb < 1) continue;
-        const int copy = round_up(alloc_rows * pitch, 128);
-        const int smem = a.n_bufs * copy + 256 + me::kRefPitch * B + me::kMaxKeys * 8 + 64;
-        if (smem > 227 * 1024) continue;
-        // small frames: keep at least ~2 CTAs per SM in flight for a 4-pair batch
-        if (!forced_tmb)
-            while (tmb > 1 && (long long)ceil_div(a.nmbx, tmb) * a.nby * (c->max_pairs > 4 ? 4 : c->max_pairs) < 2ll * c->sm_count) --tmb;
-        const bool under = smem <= smem_cap;
-        bool better;
-        if (!best_tmb) better = true;
-        else if (under != best_under_cap) better = under;
-        else if (under) better = tmb > best_tmb || (tmb == best_tmb && smem < best_smem);
-        else better = smem < best_smem;
-        if (better) { best_tmb = tmb; best_pitch = pitch; best_smem = smem; best_under_cap = under; a.copy_bytes = copy; }
+    const int forced_nsx = env_int("ME_NSX", 0), forced_nsy = env_int("ME_NSY", 0);
+    const long long work_enough = 32000;          // block-candidates per CTA beyond which a bigger CTA buys nothing
+    struct Plan { int nsx = 0, nsy = 0, su = 0, sd = 0, pitch = 0, tmb = 0, smem = 0, copy = 0, box_rows = 0, n_row_boxes = 0; long long work = 0; bool under = false; };
+    Plan best;
+    for (int tsx = 1; tsx <= 8; ++tsx) {
+        int su = tsx == 1 ? U : ((U / tsx) & ~15);
+        if (su < 16 && tsx > 1) break;
+        const int nsx = tsx == 1 ? 1 : U / su;
+        if (tsx > 1 && nsx != tsx) continue;                       // each slab count is tried once
+        if (forced_nsx && nsx != forced_nsx) continue;
+        const int wmax = U - (nsx - 1) * su;                        // the last slab is the widest
+        for (int tsy = 1; tsy <= 16; ++tsy) {
+            int sd = tsy == 1 ? U : (U / tsy) / NDY * NDY;
+            if (sd < NDY && tsy > 1) break;
+            const int nsy = tsy == 1 ? 1 : U / sd;
+            if (tsy > 1 && nsy != tsy) continue;
+            if (forced_nsy && nsy != forced_nsy) continue;
+            const int hmax = U - (nsy - 1) * sd;
+            const int win_rows = ceil_div(hmax, NDY) * NDY + B - 1;
+            const int n_row_boxes = ceil_div(win_rows, 256), box_rows = ceil_div(win_rows, n_row_boxes);
+            const int alloc_rows = n_row_boxes * box_rows;
+            for (int pi = 0; pi < 3; ++pi) {
+                const int pitch = kPitches[pi];
+                if (forced_pitch && pitch != forced_pitch) continue;
+                int tmb = (pitch - a.x_off - (wmax - 1)) / MB;
+                if (tmb > 256 / MB) tmb = 256 / MB;                 // reference strip is 256 bytes wide
+                if (tmb * NSUB > me::kMaxKeys) tmb = me::kMaxKeys / NSUB;
+                if (tmb > a.nmbx) tmb = a.nmbx;
+                if (forced_tmb) { if (forced_tmb > tmb) continue; tmb = forced_tmb; }
+                if (tmb < 1) continue;
+                // small frames: keep at least ~2 CTAs per SM in flight for a 4-pair batch
+                if (!forced_tmb)
+                    while (tmb > 1 && (long long)ceil_div(a.nmbx, tmb) * a.nby * nsx * nsy * (c->max_pairs > 4 ? 4 : c->max_pairs) < 2ll * c->sm_count) --tmb;
+                Plan p;
+                p.nsx = nsx; p.nsy = nsy; p.su = su; p.sd = sd; p.pitch = pitch; p.tmb = tmb;
+                p.box_rows = box_rows; p.n_row_boxes = n_row_boxes;
+                p.copy = round_up(alloc_rows * pitch, 128);
+                p.smem = a.n_bufs * p.copy + 256 + me::kRefPitch * B + me::kMaxKeys * 8 + 64;
+                if (p.smem > 227 * 1024) continue;
+                p.under = p.smem <= smem_cap;
+                p.work = (long long)tmb * NSUB * wmax * hmax;
+                const long long pw = p.work < work_enough ? p.work : work_enough, bw = best.work < work_enough ? best.work : work_enough;
+                bool better;
+                if (!best.tmb) better = true;
+                else if (p.under != best.under) better = p.under;
+                else if (!p.under) better = p.smem < best.smem;
+                else if ((p.nsx * p.nsy == 1) != (best.nsx * best.nsy == 1)) better = p.nsx * p.nsy == 1;   // no slabs when one window fits
+                else if (pw != bw) better = pw > bw;
+                else if (p.nsx * p.nsy != best.nsx * best.nsy) better = p.nsx * p.nsy < best.nsx * best.nsy;
+                else if (p.tmb != best.tmb) better = p.tmb > best.tmb;
+                else better = p.smem < best.smem;
+                if (better) best = p;
+            }
+        }
     }
-    if (!best_tmb)
-        return fail(ME_EUNSUPPORTED, "block %d with range %d: the %d-byte window row (or its %d-row copies) does not fit one "
-                    "TMA box / 227 KB of shared memory", B, R, a.x_off + MB + 2 * R, alloc_rows);
-    a.tmb = best_tmb;
-    c->win_pitch = best_pitch;
-    c->smem = best_smem;
-    c->kc = pick_kernel(B, best_pitch, k64);
+    if (!best.tmb)
+        return fail(ME_EUNSUPPORTED, "block %d with range %d: no slab of the candidate square fits one TMA box and 227 KB of "
+                    "shared memory", B, R);
+    a.nsx = best.nsx; a.nsy = best.nsy; a.su = best.su; a.sd = best.sd;
+    a.tmb = best.tmb; a.copy_bytes = best.copy; a.box_rows = best.box_rows; a.n_row_boxes = best.n_row_boxes;
+    c->win_pitch = best.pitch;
+    c->smem = best.smem;
+    c->kc = pick_kernel(B, best.pitch, k64);
     a.tiles_x = ceil_div(a.nmbx, a.tmb);
     a.tiles_per_pair = a.tiles_x * a.nby;
 
+    // candidate tiling inside a slab of width w: per shift s the columns q with 4q + s < w, in NQ-wide
+    // groups (16-byte aligned starts) plus single leftover columns.  Table 0: regular slab, 1: last slab.
+    for (int t = 0; t < 2; ++t) {
+        const int w = t == 0 ? (a.nsx > 1 ? a.su : U) : U - (a.nsx - 1) * a.su;
+        int ng = 0;
+        a.n_wide[t] = a.n_narrow[t] = 0;
+        for (int pass = 0; pass < 2; ++pass)
+            for (int s = 0; s < 4; ++s) {
+                const int nq = (w - 1 - s) >= 0 ? (w - 1 - s) / 4 + 1 : 0;
+                const int nwide = nq / NQ;
+                if (pass == 0) {
+                    for (int g = 0; g < nwide; ++g, ++ng, ++a.n_wide[t]) {
+                        if (ng >= me::kMaxGroups) return fail(ME_EUNSUPPORTED, "range %d needs more than %d column groups", R, me::kMaxGroups);
+                        a.group[t][ng] = (unsigned short)((s << 12) | (g * NQ));
+                    }
+                } else {
+                    for (int q = nwide * NQ; q < nq; ++q, ++ng, ++a.n_narrow[t]) {
+                        if (ng >= me::kMaxGroups) return fail(ME_EUNSUPPORTED, "range %d needs more than %d column groups", R, me::kMaxGroups);
+                        a.group[t][ng] = (unsigned short)((s << 12) | q);
+                    }
+                }
+            }
+    }
+
     // Threads: whole multiples of 4 warps so that every scheduler of the SM gets the same number of warps
     // (r01 sweep: 224 threads = 7 warps ran 13 % slower than 128 or 256).
-    const int total = a.tmb * a.ndyg * a.n_wide;
+    const int total = a.tmb * ceil_div(U - (a.nsy - 1) * a.sd, NDY) * a.n_wide[1];
     c->threads = env_int("ME_THREADS", total >= 512 ? 256 : 128);
     if (c->threads % 32 || c->threads < 32 || c->threads > c->kc.maxt)
         return fail(ME_EINVAL, "ME_THREADS=%d is not a multiple of 32 in [32,%d]", c->threads, c->kc.maxt);
@@ -279,7 +309,7 @@ int launch_search(me_ctx *c, const uint8_t *frames, const CUtensorMap &tm_win, c
     a.pairs = c->d_pairs;
     void *params[3] = {(void *)&tm_win, (void *)&tm_ref, (void *)&a};
     CU_TRY(cudaEventRecord(c->ev_k0, st));
-    CU_TRY(cudaLaunchKernel(c->kc.fn, dim3((unsigned)(a.tiles_per_pair * n_pairs)), dim3((unsigned)c->threads), params,
+    CU_TRY(cudaLaunchKernel(c->kc.fn, dim3((unsigned)(a.tiles_per_pair * n_pairs * a.nsx * a.nsy)), dim3((unsigned)c->threads), params,
                             (size_t)c->smem, st));
     CU_TRY(cudaEventRecord(c->ev_k1, st));
     c->launches += 1;
@@ -437,6 +467,13 @@ int me_create(int device, int height, int width, const me_params *params, int ma
     CREATE_TRY(cudaMalloc(&c->args.pair_out, sizeof(me_pair_result) * (size_t)max_pairs));
     CREATE_TRY(cudaMalloc(&c->args.pair_ticket, sizeof(unsigned) * (size_t)max_pairs));
     CREATE_TRY(cudaMemset(c->args.pair_ticket, 0, sizeof(unsigned) * (size_t)max_pairs));
+    if (c->args.nsx * c->args.nsy > 1) {          // cross-slab argmin scratch: all-ones keys, zero tickets (self-restoring)
+        const size_t nt = (size_t)c->args.tiles_per_pair * (size_t)max_pairs;
+        CREATE_TRY(cudaMalloc(&c->args.blk_key, nb * sizeof(unsigned long long)));
+        CREATE_TRY(cudaMemset(c->args.blk_key, 0xff, nb * sizeof(unsigned long long)));
+        CREATE_TRY(cudaMalloc(&c->args.tile_ticket, nt * sizeof(unsigned)));
+        CREATE_TRY(cudaMemset(c->args.tile_ticket, 0, nt * sizeof(unsigned)));
+    }
     CREATE_TRY(cudaFuncSetAttribute(c->kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, c->smem));
     CREATE_TRY(cudaFuncSetAttribute(c->kc.fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
 #undef CREATE_TRY
@@ -455,7 +492,7 @@ int me_destroy(me_ctx *c)
     if (c->s_compute) cudaStreamSynchronize(c->s_compute);
     cudaFree(c->d_frames); cudaFree(c->d_bgr); cudaFree(c->d_pairs);
     cudaFree(c->args.blk_mv); cudaFree(c->args.blk_sad); cudaFree(c->args.blk_sub); cudaFree(c->args.blk_flags);
-    cudaFree(c->args.pair_out); cudaFree(c->args.pair_ticket);
+    cudaFree(c->args.pair_out); cudaFree(c->args.pair_ticket); cudaFree(c->args.blk_key); cudaFree(c->args.tile_ticket);
     for (int i = 0; i < 2; ++i) {
         if (c->h_stage[i]) cudaFreeHost(c->h_stage[i]);
         if (c->stage_free[i]) cudaEventDestroy(c->stage_free[i]);
@@ -485,6 +522,7 @@ int me_get_geometry(const me_ctx *c, me_geometry *g)
     g->tiles_per_pair = c->args.tiles_per_pair;
     g->cand_px_per_pair = c->cand_px; g->cand_px_per_pair_valid = c->cand_px_valid;
     g->sm_count = c->sm_count; g->uses_tma = c->args.use_tma;
+    g->slabs_x = c->args.nsx; g->slabs_y = c->args.nsy; g->window_pitch = c->win_pitch; g->reserved = 0;
     return ME_OK;
 }
 
@@ -763,15 +801,19 @@ extern "C" int me_search_static_scratch(const uint8_t *d_frames, size_t pitch, i
     rc = configure(&plan);
     if (rc) return rc;
 
-    // Carve the static array: tickets | pairs | mv | sad | sub | flags
+    // Carve the static array: tickets | pairs | mv | sad | sub | flags | (slabbed searches: tile tickets | keys)
     const size_t nb = (size_t)plan.args.nb * (size_t)n_pairs;
+    const bool slabbed = plan.args.nsx * plan.args.nsy > 1;
+    const size_t nt = (size_t)plan.args.tiles_per_pair * (size_t)n_pairs;
     const size_t o_ticket = 0;
     const size_t o_pairs = o_ticket + align256(sizeof(unsigned) * (size_t)n_pairs);
     const size_t o_mv = o_pairs + align256(sizeof(int32_t) * 2 * (size_t)n_pairs);
     const size_t o_sad = o_mv + align256(nb * 2 * sizeof(int16_t));
     const size_t o_sub = o_sad + align256(nb * sizeof(uint32_t));
     const size_t o_flags = o_sub + align256(nb * 2 * sizeof(float));
-    const size_t need = o_flags + align256(nb);
+    const size_t o_tt = o_flags + align256(nb);
+    const size_t o_key = o_tt + (slabbed ? align256(nt * sizeof(unsigned)) : 0);
+    const size_t need = o_key + (slabbed ? align256(nb * sizeof(unsigned long long)) : 0);
     if (need > (size_t)ME_STATIC_SCRATCH_BYTES)
         return fail(ME_EINVAL, "%d pair(s) of %d blocks need %zu bytes of working memory; the static array holds %u "
                     "(ME_STATIC_SCRATCH_BYTES). Split the batch or use a context (me_create / me_search_device).",
@@ -795,11 +837,18 @@ extern "C" int me_search_static_scratch(const uint8_t *d_frames, size_t pitch, i
     a.blk_sub = reinterpret_cast<float *>(base + o_sub);
     a.blk_flags = base + o_flags;
     a.pair_out = d_out;
-    // the tickets must start at zero; the rest of the array is written before it is read
+    // the tickets must start at zero (and, for slabbed searches, the keys at all-ones); the rest of the
+    // array is written before it is read
     CU_TRY(cudaMemsetAsync(base + o_ticket, 0, sizeof(unsigned) * (size_t)n_pairs, st));
+    if (slabbed) {
+        a.tile_ticket = reinterpret_cast<unsigned int *>(base + o_tt);
+        a.blk_key = reinterpret_cast<unsigned long long *>(base + o_key);
+        CU_TRY(cudaMemsetAsync(base + o_tt, 0, nt * sizeof(unsigned), st));
+        CU_TRY(cudaMemsetAsync(base + o_key, 0xff, nb * sizeof(unsigned long long), st));
+    }
     CU_TRY(cudaMemcpyAsync(base + o_pairs, pairs, sizeof(int32_t) * 2 * (size_t)n_pairs, cudaMemcpyHostToDevice, st));
     void *kargs[3] = {(void *)&tw, (void *)&tr, (void *)&a};
-    CU_TRY(cudaLaunchKernel(plan.kc.fn, dim3((unsigned)(a.tiles_per_pair * n_pairs)), dim3((unsigned)plan.threads), kargs,
+    CU_TRY(cudaLaunchKernel(plan.kc.fn, dim3((unsigned)(a.tiles_per_pair * n_pairs * a.nsx * a.nsy)), dim3((unsigned)plan.threads), kargs,
                             (size_t)plan.smem, st));
     return ME_OK;
 }

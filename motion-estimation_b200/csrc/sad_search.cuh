@@ -20,8 +20,8 @@
 //             Columns that do not fill an NQ-wide patch run as NDY x 1 patches afterwards.
 //   argmin    key = (sad << RB) | rank, rank = (dy+R)*(2R+1) + (dx+R): the minimum key is the
 //             first minimum in raster order whatever the reduction order (spec tie-break).
-//   finalize  one warp per block recomputes the four neighbour SADs from global memory, applies
-//             the parabola fit and the gates and writes the per-block record.
+//   finalize  eight lanes per block recompute the four neighbour SADs from global memory, apply
+//             the parabola fit and the gates and write the per-block record.
 //   reduce    the last CTA of a pair (atomic ticket) radix-selects the per-axis medians.
 //
 // The spec this implements is written down in oracle/sad_oracle.c; reference call sites replaced:
@@ -64,11 +64,17 @@ struct SearchArgs {
     int box_rows, n_row_boxes;
     int x_off;                  // (X0 - R) - (16-byte aligned TMA x origin), 0..15
     int n_bufs;                 // 4 when x_off == 0 (TMA lands in copy 0), else 5 (raw + 4 copies)
-    // candidate tiling: column groups [0, n_wide) are NQ wide, [n_wide, n_wide + n_narrow) one column
-    int ndyg;                   // ceil(U / NDY)
-    int n_wide, n_narrow;
-    unsigned short group[kMaxGroups];   // (s << 12) | q0
-    unsigned magic_ndyg;        // fastdiv_magic(ndyg)
+    // candidate slabs: the (2R+1)^2 candidate square is cut into nsx x nsy rectangles, one CTA each, so
+    // that a window never exceeds one TMA box / the shared-memory budget.  Slab (sx,sy) starts at
+    // (u, dyi) = (sx*su, sy*sd); the last slab of each axis takes the remainder (it is the largest).
+    int nsx, nsy, su, sd;
+    // candidate tiling inside a slab: column groups [0, n_wide) are NQ wide, then n_narrow single columns.
+    // Index 0 = regular slab, 1 = last slab in x.
+    int n_wide[2], n_narrow[2];
+    unsigned short group[2][kMaxGroups];   // (s << 12) | q0
+    // cross-slab argmin (only when nsx*nsy > 1): all-ones on entry, restored by the finalizing CTA
+    unsigned long long *blk_key;   // [P][nb]
+    unsigned int *tile_ticket;     // [P][tiles_per_pair] zero on entry, reset by the finalizing CTA
     // gates
     int min_range, min_curv, subpixel, min_valid;
     int use_tma;
@@ -216,11 +222,13 @@ __device__ __forceinline__ float funkey(uint32_t k)
     return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
 }
 
-// One warp: neighbour SADs, gates, parabola, per-block record.
+// Eight lanes (one quarter of a warp, `mask` names them, `lane` = 0..7 inside the group): neighbour SADs,
+// gates, parabola, per-block record.  Four blocks are finalized per warp pass.
+constexpr int kFinLanes = 8;
 template <int B>
 __device__ __forceinline__ void finalize_block(const SearchArgs &a, int pair, const uint8_t *prevf,
                                                const uint8_t *curf, int bx, int by, uint32_t sad, uint32_t rank,
-                                               int lane)
+                                               int lane, unsigned mask)
 {
     constexpr int SW = B / 4;
     const int R = a.R, U = a.U, x0 = bx * B, y0 = by * B;
@@ -232,7 +240,7 @@ __device__ __forceinline__ void finalize_block(const SearchArgs &a, int pair, co
     const bool yin = dy - 1 >= dylo && dy + 1 <= dyhi;
     const size_t pitch = (size_t)a.frame_pitch;
     uint32_t sxm = 0, sxp = 0, sym = 0, syp = 0, vmn = 0xffffffffu, vmx = 0u;
-    for (int idx = lane; idx < B * SW; idx += 32) {
+    for (int idx = lane; idx < B * SW; idx += kFinLanes) {
         const int row = idx / SW, wd = idx - row * SW;
         const uint32_t rw = __ldg(reinterpret_cast<const uint32_t *>(prevf + (size_t)(y0 + row) * pitch + x0) + wd);
         vmn = __vminu4(vmn, rw);
@@ -247,12 +255,12 @@ __device__ __forceinline__ void finalize_block(const SearchArgs &a, int pair, co
             syp = vsad4(rw, ld_bytes4(c + pitch), syp);
         }
     }
-    sxm = __reduce_add_sync(kFull, sxm);
-    sxp = __reduce_add_sync(kFull, sxp);
-    sym = __reduce_add_sync(kFull, sym);
-    syp = __reduce_add_sync(kFull, syp);
-    const uint32_t mn = __reduce_min_sync(kFull, hmin_bytes(vmn));
-    const uint32_t mx = __reduce_max_sync(kFull, hmax_bytes(vmx));
+    sxm = __reduce_add_sync(mask, sxm);
+    sxp = __reduce_add_sync(mask, sxp);
+    sym = __reduce_add_sync(mask, sym);
+    syp = __reduce_add_sync(mask, syp);
+    const uint32_t mn = __reduce_min_sync(mask, hmin_bytes(vmn));
+    const uint32_t mx = __reduce_max_sync(mask, hmax_bytes(vmx));
     if (lane == 0) {
         unsigned flags = 0;
         if ((int)(mx - mn) >= a.min_range) flags |= ME_FLAG_TEXTURED;
@@ -395,7 +403,7 @@ template <int B, int NDY, int NQP, int PITCH, int LW, bool K64, int RB>
 __device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j, int dyg, int s, int q0,
                                          const uint8_t *s_win, const uint8_t *s_ref,
                                          typename KeyOf<K64>::T *s_key, bool tile_interior, int dyi_lo, int dyi_hi,
-                                         int X0, int lane)
+                                         int X0, int lane, int ubase, int dbase, int slab_w)
 {
     using KeyT = typename KeyOf<K64>::T;
     using G = Geo<B>;
@@ -421,16 +429,16 @@ __device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j
         const uint32_t *ref = reinterpret_cast<const uint32_t *>(s_ref) + j * G::BW;
         sad_patch<B, NDY, NQP, PITCH, LW>(cur, ref, acc);
 
-        const int dyi0 = dyg * NDY, u0 = 4 * q0 + s, twoR = 2 * a.R;
-        // domain of each block in index space (u = dx + R, dyi = dy + R)
+        // everything below is in SLAB-LOCAL index space: u = dx + R - ubase, dyi = dy + R - dbase
+        const int dyi0 = dyg * NDY, u0 = 4 * q0 + s;
         int u_lo[G::NSUB], u_hi[G::NSUB];
         bool whole = dyi0 >= dyi_lo && dyi0 + NDY - 1 <= dyi_hi;
 #pragma unroll
         for (int sb = 0; sb < G::NSUB; ++sb) {
-            u_lo[sb] = 0; u_hi[sb] = twoR;
+            u_lo[sb] = 0; u_hi[sb] = slab_w - 1;
             if (!tile_interior) {
                 const int x0 = X0 + j * G::MB + sb * B;
-                u_lo[sb] = max(0, a.R - x0); u_hi[sb] = min(twoR, a.R + a.W - B - x0);
+                u_lo[sb] = max(0, a.R - x0 - ubase); u_hi[sb] = min(slab_w - 1, min(2 * a.R, a.R + a.W - B - x0) - ubase);
                 whole = whole && u0 >= u_lo[sb] && u0 + 4 * (NQP - 1) <= u_hi[sb];
             }
         }
@@ -466,7 +474,7 @@ __device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j
             if (lk[sb] != 0xffffffffu) {
                 const uint32_t sad = lk[sb] / KM;
                 const int idx = (int)(lk[sb] - sad * KM), d = idx / NQP, q = idx - d * NQP;
-                const uint32_t rank = (uint32_t)((dyi0 + d) * a.U + u0 + 4 * q);
+                const uint32_t rank = (uint32_t)((dbase + dyi0 + d) * a.U + ubase + u0 + 4 * q);
                 best[sb] = ((KeyT)sad << RB) | (KeyT)rank;
             }
         }
@@ -498,9 +506,15 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     extern __shared__ __align__(1024) uint8_t smem[];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
-    const int pair = blockIdx.x / a.tiles_per_pair;
-    const int tr = blockIdx.x - pair * a.tiles_per_pair;
+    const int nslab = a.nsx * a.nsy;
+    const int tile_id = blockIdx.x / nslab, slab = blockIdx.x - tile_id * nslab;   // slabs of a tile are adjacent CTAs
+    const int pair = tile_id / a.tiles_per_pair;
+    const int tr = tile_id - pair * a.tiles_per_pair;
     const int ty = tr / a.tiles_x, tx = tr - ty * a.tiles_x;
+    const int sy = slab / a.nsx, sx = slab - sy * a.nsx;
+    const int ubase = sx * a.su, dbase = sy * a.sd;
+    const int lastx = sx == a.nsx - 1;
+    const int slab_w = lastx ? a.U - ubase : a.su, slab_h = (sy == a.nsy - 1) ? a.U - dbase : a.sd;
     const int prev_slot = __ldg(a.pairs + 2 * pair), cur_slot = __ldg(a.pairs + 2 * pair + 1);
     const int X0 = tx * a.tmb * G::MB, Y0 = ty * B;
     const int nj = min(a.tmb, a.nmbx - tx * a.tmb);                    // macro-blocks in this tile
@@ -514,17 +528,29 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_ref + ref_bytes + kMaxKeys * 8);
     int *s_last = reinterpret_cast<int *>(s_bar + 1);
 
+    // ---- this slab's share of the block row's domain, in slab-local index space.  dy groups that lie wholly
+    //      outside it are not enumerated at all (most of the work on the 64-pixel-tall recordings), and a slab
+    //      with none loads nothing.
+    const int twoR = 2 * a.R;
+    const int dyi_lo = max(0, a.R - Y0 - dbase), dyi_hi = min(slab_h - 1, min(twoR, a.R + a.H - B - Y0) - dbase);
+    const int xlast = X0 + (nblk - 1) * B;
+    const bool tile_interior = dyi_lo == 0 && dyi_hi == slab_h - 1 && a.R - X0 - ubase <= 0 &&
+                               min(twoR, a.R + a.W - B - xlast) - ubase >= slab_w - 1;
+    const int dyg_lo = dyi_lo / NDY, dyg_hi = dyi_hi >= 0 ? dyi_hi / NDY : -1;
+    const int nd = dyi_hi >= dyi_lo ? dyg_hi - dyg_lo + 1 : 0;         // 0: this slab holds no candidate of this block row
     if (tid < kMaxKeys) s_key[tid] = kNone;
 
-    const int wx0 = X0 - a.R - a.x_off;                               // multiple of 16
-    if (a.use_tma) {
+    const int wx0 = X0 - a.R - a.x_off + ubase, wy0 = Y0 - a.R + dbase;   // wx0 is a multiple of 16 (su is)
+    if (nd == 0) {
+        __syncthreads();                                               // s_key initialised; nothing to load or search
+    } else if (a.use_tma) {
         if (tid == 0) mbar_init(s_bar, 1);
         __syncthreads();
         if (tid == 0) {
             const uint32_t bytes = (uint32_t)a.n_row_boxes * a.box_rows * PITCH + (uint32_t)ref_bytes;
             mbar_expect_tx(s_bar, bytes);
             for (int rb = 0; rb < a.n_row_boxes; ++rb)
-                tma_load_3d(s_raw + (size_t)rb * a.box_rows * PITCH, &tm_win, wx0, Y0 - a.R + rb * a.box_rows,
+                tma_load_3d(s_raw + (size_t)rb * a.box_rows * PITCH, &tm_win, wx0, wy0 + rb * a.box_rows,
                             cur_slot, s_bar);
             tma_load_3d(s_ref, &tm_ref, X0, Y0, prev_slot, s_bar);
         }
@@ -536,7 +562,7 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
         const int rows = a.n_row_boxes * a.box_rows;
         for (int i = tid; i < rows * PITCH; i += blockDim.x) {
             const int r = i / PITCH, c = i - r * PITCH;
-            const int gx = wx0 + c, gy = Y0 - a.R + r;
+            const int gx = wx0 + c, gy = wy0 + r;
             uint8_t v = 0;
             if (gx >= 0 && gx < a.W && gy >= 0 && gy < a.H) v = curf[(size_t)gy * a.frame_pitch + gx];
             s_raw[i] = v;
@@ -550,7 +576,7 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     }
 
     // ---- derive the byte-shifted copies: copy s, byte k of a row = raw byte (x_off + s + k)
-    {
+    if (nd > 0) {
         const int chunks = a.n_row_boxes * a.box_rows * (PITCH >> 4);   // 16-byte chunks per copy
         const uint32_t *raw = reinterpret_cast<const uint32_t *>(s_raw);
         if (a.x_off == 0) {                                             // copy 0 is the TMA destination itself
@@ -594,16 +620,12 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
         __syncthreads();
     }
 
-    // ---- candidate patches.  dy groups that lie wholly outside this block row's domain are not
-    //      enumerated at all (they are most of the work on the 64-pixel-tall example recordings).
-    const int twoR = 2 * a.R;
-    const int dyi_lo = max(0, a.R - Y0), dyi_hi = min(twoR, a.R + a.H - B - Y0);
-    const bool tile_interior = dyi_lo == 0 && dyi_hi == twoR && X0 - a.R >= 0 && X0 + nblk * B + a.R <= a.W;
-    const int dyg_lo = dyi_lo / NDY, dyg_hi = dyi_hi / NDY;
-    const int nd = dyg_hi - dyg_lo + 1;
-    const unsigned magic_nd = nd == a.ndyg ? a.magic_ndyg : fastdiv_magic((unsigned)nd);
-    {   // wide patches: NDY x NQ
-        const int per_j = nd * a.n_wide;
+    // ---- candidate patches
+    const unsigned magic_nd = fastdiv_magic((unsigned)nd);
+    const unsigned short *grp = a.group[lastx];
+    const int n_wide = a.n_wide[lastx], n_narrow = a.n_narrow[lastx];
+    if (nd > 0) {   // wide patches: NDY x NQ
+        const int per_j = nd * n_wide;
         const int total = nj * per_j;
         const unsigned magic_pj = fastdiv_magic((unsigned)per_j);
         const int iters = (total + (int)blockDim.x - 1) / (int)blockDim.x;
@@ -613,13 +635,13 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
             const int w = active ? w_raw : total - 1;
             const int j = fastdiv(w, magic_pj), r = w - j * per_j;
             const int cg = fastdiv(r, magic_nd), dyg = dyg_lo + r - cg * nd;   // dy group varies fastest across lanes
-            const unsigned g = a.group[cg];
+            const unsigned g = grp[cg];
             run_item<B, NDY, NQ, PITCH, LWW, K64, RB>(a, active, j, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
-                                                      s_key, tile_interior, dyi_lo, dyi_hi, X0, lane);
+                                                      s_key, tile_interior, dyi_lo, dyi_hi, X0, lane, ubase, dbase, slab_w);
         }
     }
-    if (a.n_narrow > 0) {   // leftover columns: NDY x 1
-        const int per_j = nd * a.n_narrow;
+    if (nd > 0 && n_narrow > 0) {   // leftover columns: NDY x 1
+        const int per_j = nd * n_narrow;
         const int total = nj * per_j;
         const unsigned magic_pj = fastdiv_magic((unsigned)per_j);
         const int iters = (total + (int)blockDim.x - 1) / (int)blockDim.x;
@@ -629,22 +651,47 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
             const int w = active ? w_raw : total - 1;
             const int j = fastdiv(w, magic_pj), r = w - j * per_j;
             const int cg = fastdiv(r, magic_nd), dyg = dyg_lo + r - cg * nd;
-            const unsigned g = a.group[a.n_wide + cg];
+            const unsigned g = grp[n_wide + cg];
             run_item<B, NDY, 1, PITCH, 1, K64, RB>(a, active, j, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
-                                                   s_key, tile_interior, dyi_lo, dyi_hi, X0, lane);
+                                                   s_key, tile_interior, dyi_lo, dyi_hi, X0, lane, ubase, dbase, slab_w);
         }
     }
     __syncthreads();
+
+    // ---- several slabs per tile: fold this CTA's block minima into the global keys; the CTA that
+    //      arrives last at the tile's ticket owns the finalize step.
+    if (nslab > 1) {
+        const size_t kbase = (size_t)pair * a.nb + (size_t)ty * a.nbx + (size_t)tx * a.tmb * G::NSUB;
+        KeyT *gkey = reinterpret_cast<KeyT *>(a.blk_key);               // 8 bytes reserved per block, KeyT used
+        if (tid < nblk && s_key[tid] != kNone) atomicMin(&gkey[kbase + tid], s_key[tid]);
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) {
+            const unsigned old = atomicAdd(&a.tile_ticket[tile_id], 1u);
+            *s_last = (old == (unsigned)nslab - 1u);
+        }
+        __syncthreads();
+        if (!*s_last) return;
+        __threadfence();
+        if (tid < nblk) {
+            s_key[tid] = __ldcg(&gkey[kbase + tid]);
+            gkey[kbase + tid] = kNone;                                  // leave the scratch as we found it
+        }
+        if (tid == 0) a.tile_ticket[tile_id] = 0;
+        __syncthreads();
+    }
 
     // ---- per-block finalize (one warp per block)
     {
         const uint8_t *curf = a.frames + (long long)cur_slot * a.frame_stride;
         const uint8_t *prevf = a.frames + (long long)prev_slot * a.frame_stride;
         constexpr KeyT rmask = (KeyT(1) << RB) - 1;
-        for (int jb = warp; jb < nblk; jb += nwarps) {
+        constexpr int per_warp = 32 / kFinLanes;
+        const int grp = lane / kFinLanes;
+        for (int jb = warp * per_warp + grp; jb < nblk; jb += nwarps * per_warp) {
             const KeyT key = s_key[jb];
             finalize_block<B>(a, pair, prevf, curf, tx * a.tmb * G::NSUB + jb, ty, (uint32_t)(key >> RB),
-                              (uint32_t)(key & rmask), lane);
+                              (uint32_t)(key & rmask), lane % kFinLanes, ((1u << kFinLanes) - 1u) << (grp * kFinLanes));
         }
     }
     __syncthreads();

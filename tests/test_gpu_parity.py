@@ -33,6 +33,7 @@ CASES = [
     (64, 96, 16, 8), (64, 640, 16, 32), (70, 100, 16, 8), (72, 200, 8, 12), (96, 160, 32, 16),
     (270, 480, 16, 32), (136, 256, 8, 64), (48, 64, 16, 1), (33, 47, 16, 5), (64, 128, 32, 40),
     (80, 144, 16, 50), (16, 16, 16, 4), (40, 336, 8, 7), (128, 128, 16, 96),
+    (160, 192, 16, 100), (144, 304, 16, 127), (72, 136, 8, 90), (200, 168, 32, 72),   # ranges that need candidate slabs
 ]
 
 
@@ -96,6 +97,24 @@ def test_plain_loader_equals_tma_loader(me, monkeypatch):
     assert out[0][0] == out[1][0]
     for k in KEYS:
         np.testing.assert_array_equal(out[0][1][k], out[1][1][k])
+
+
+@pytest.mark.parametrize("nsx,nsy", [(1, 2), (2, 1), (2, 3), (1, 7)])
+def test_candidate_slabs_do_not_change_results(me, monkeypatch, nsx, nsy):
+    """Force the candidate square to be cut into several CTAs per tile (cross-CTA argmin through global keys)."""
+    from motion_estimation_b200 import synth
+    frames, _ = synth.translating_frames(3, 112, 240, 30)
+    cfg = me.SearchConfig(block=16, range=36)
+    monkeypatch.setenv("ME_NSX", str(nsx))
+    monkeypatch.setenv("ME_NSY", str(nsy))
+    with me.MotionEstimator(112, 240, cfg, max_frames=3, max_pairs=3) as est:
+        assert (est.geometry["slabs_x"], est.geometry["slabs_y"]) == (nsx, nsy)
+        est.upload(frames)
+        pairs = [(0, 1), (1, 2), (2, 0)]
+        for _ in range(2):                                  # twice: the global keys and tickets must be left clean
+            res = est.search(pairs)
+            for i, (a, c) in enumerate(pairs):
+                check_pair(est, i, frames[a], frames[c], cfg, res[i])
 
 
 @pytest.mark.parametrize("tbx", [1, 2, 4, 8])
@@ -172,7 +191,7 @@ def test_errors_are_reported_not_swallowed(me):
             est.upload(np.zeros((1, 32, 128), np.uint8))    # wrong frame height
     with pytest.raises(me.MEError) as e:
         me.MotionEstimator(64, 128, me.SearchConfig(16, 128))
-    assert e.value.code == -2 and "range" in str(e.value)   # one TMA box per window: documented limit
+    assert e.value.code == -2 and "range" in str(e.value)   # candidate rank is 16 bits: range <= 127
 
 
 # ----------------------------------------------------------------------------- BASELINE sizes

@@ -52,6 +52,26 @@ def test_static_scratch_entry_point_equals_context_entry_point(me):
             assert want["flag"].all() and want["nvalid_x"].min() > 10
 
 
+def test_static_scratch_with_candidate_slabs(me):
+    """A range large enough to be cut into several CTAs per tile uses two more pieces of the shared array."""
+    import torch
+    from motion_estimation_b200 import synth
+    H, W = 96, 208
+    cfg = me.SearchConfig(block=16, range=100)
+    stream = torch.cuda.current_stream().cuda_stream
+    frames, _ = synth.translating_frames(3, H, W, 24)
+    t = torch.from_numpy(frames).cuda().contiguous()
+    pairs = [(0, 1), (1, 2)]
+    with me.MotionEstimator(H, W, cfg, max_frames=2, max_pairs=2) as est:
+        assert est.geometry["slabs_x"] * est.geometry["slabs_y"] > 1
+        for _ in range(2):
+            out = torch.zeros(len(pairs) * 6, dtype=torch.int32, device="cuda")
+            assert _static_search(me, t, pairs, cfg, out, stream) == 0, me._lib.lib().me_last_error()
+            torch.cuda.synchronize()
+            est.search_device(t.data_ptr(), t.stride(1), t.shape[0], pairs, stream=stream)
+            assert out.cpu().numpy().view(me.PAIR_DTYPE).tobytes() == est.fetch_pairs(len(pairs)).tobytes()
+
+
 def test_static_scratch_rejects_oversized_requests(me):
     import torch
     L = me._lib.lib()
