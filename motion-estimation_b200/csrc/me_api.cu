@@ -188,7 +188,7 @@ int configure(me_ctx *c)
     const int forced_tmb = env_int("ME_TBX", 0), forced_pitch = env_int("ME_PITCH", 0);
     const int forced_nsx = env_int("ME_NSX", 0), forced_nsy = env_int("ME_NSY", 0);
     const long long work_enough = 32000;          // block-candidates per CTA beyond which a bigger CTA buys nothing
-    struct Plan { int nsx = 0, nsy = 0, su = 0, sd = 0, pitch = 0, tmb = 0, smem = 0, copy = 0, box_rows = 0, n_row_boxes = 0; long long work = 0; bool under = false; };
+    struct Plan { int nsx = 0, nsy = 0, su = 0, sd = 0, pitch = 0, tmb = 0, smem = 0, copy = 0, box_rows = 0, n_row_boxes = 0; long long work = 0; bool under = false; double balance = 0; };
     Plan best;
     for (int tsx = 1; tsx <= 8; ++tsx) {
         int su = tsx == 1 ? U : ((U / tsx) & ~15);
@@ -219,25 +219,36 @@ int configure(me_ctx *c)
                 // small frames: keep at least ~2 CTAs per SM in flight for a 4-pair batch
                 if (!forced_tmb)
                     while (tmb > 1 && (long long)ceil_div(a.nmbx, tmb) * a.nby * nsx * nsy * (c->max_pairs > 4 ? 4 : c->max_pairs) < 2ll * c->sm_count) --tmb;
-                Plan p;
-                p.nsx = nsx; p.nsy = nsy; p.su = su; p.sd = sd; p.pitch = pitch; p.tmb = tmb;
-                p.box_rows = box_rows; p.n_row_boxes = n_row_boxes;
-                p.copy = round_up(alloc_rows * pitch, 128);
-                p.smem = a.n_bufs * p.copy + 256 + me::kRefPitch * B + me::kMaxKeys * 8 + 64;
-                if (p.smem > 227 * 1024) continue;
-                p.under = p.smem <= smem_cap;
-                p.work = (long long)tmb * NSUB * wmax * hmax;
-                const long long pw = p.work < work_enough ? p.work : work_enough, bw = best.work < work_enough ? best.work : work_enough;
-                bool better;
-                if (!best.tmb) better = true;
-                else if (p.under != best.under) better = p.under;
-                else if (!p.under) better = p.smem < best.smem;
-                else if ((p.nsx * p.nsy == 1) != (best.nsx * best.nsy == 1)) better = p.nsx * p.nsy == 1;   // no slabs when one window fits
-                else if (pw != bw) better = pw > bw;
-                else if (p.nsx * p.nsy != best.nsx * best.nsy) better = p.nsx * p.nsy < best.nsx * best.nsy;
-                else if (p.tmb != best.tmb) better = p.tmb > best.tmb;
-                else better = p.smem < best.smem;
-                if (better) best = p;
+                // every tile width from the widest that fits down to half of it: a narrower tile can
+                // divide its work items over the CTA's warps more evenly (r01: 8 blocks beat 9 by 1.2 %)
+                const int tmb_lo = forced_tmb ? tmb : (tmb + 1) / 2;
+                for (int t = tmb; t >= tmb_lo; --t) {
+                    Plan p;
+                    p.nsx = nsx; p.nsy = nsy; p.su = su; p.sd = sd; p.pitch = pitch; p.tmb = t;
+                    p.box_rows = box_rows; p.n_row_boxes = n_row_boxes;
+                    p.copy = round_up(alloc_rows * pitch, 128);
+                    p.smem = a.n_bufs * p.copy + 256 + me::kRefPitch * B + me::kMaxKeys * 8 + 64;
+                    if (p.smem > 227 * 1024) continue;
+                    p.under = p.smem <= smem_cap;
+                    p.work = (long long)t * NSUB * wmax * hmax;
+                    // work items of a full tile over 256 threads: fraction of warp passes that are full
+                    const int nqw = ((wmax - 1) / 4 + 1) / NQ + 3 * (((wmax - 2) / 4 + 1) / NQ);   // ~ wide column groups
+                    const long long items = (long long)t * ceil_div(hmax, NDY) * (nqw > 0 ? nqw : 1);
+                    p.balance = (double)items / (double)(ceil_div((int)items, 256) * 256)
+                              * (double)a.nmbx / (double)(ceil_div(a.nmbx, t) * t);      // ... and of tiles that are full
+                    const long long pw = p.work < work_enough ? p.work : work_enough, bw = best.work < work_enough ? best.work : work_enough;
+                    bool better;
+                    if (!best.tmb) better = true;
+                    else if (p.under != best.under) better = p.under;
+                    else if (!p.under) better = p.smem < best.smem;
+                    else if ((p.nsx * p.nsy == 1) != (best.nsx * best.nsy == 1)) better = p.nsx * p.nsy == 1;   // no slabs when one window fits
+                    else if (pw != bw) better = pw > bw;
+                    else if (p.balance > best.balance + 0.015 || p.balance < best.balance - 0.015) better = p.balance > best.balance;
+                    else if (p.nsx * p.nsy != best.nsx * best.nsy) better = p.nsx * p.nsy < best.nsx * best.nsy;
+                    else if (p.tmb != best.tmb) better = p.tmb > best.tmb;
+                    else better = p.smem < best.smem;
+                    if (better) best = p;
+                }
             }
         }
     }
@@ -274,6 +285,19 @@ int configure(me_ctx *c)
                     }
                 }
             }
+    }
+
+    {   // fastdiv magics of full slabs (see sad_search.cuh)
+        auto magic = [](int d) { return d <= 1 ? 0u : (unsigned)(0x100000000ull / (unsigned)d + 1ull); };
+        for (int ly = 0; ly < 2; ++ly) {
+            const int h = ly == 0 ? (a.nsy > 1 ? a.sd : U) : U - (a.nsy - 1) * a.sd;
+            a.full_nd[ly] = ceil_div(h, NDY);
+            a.magic_nd[ly] = magic(a.full_nd[ly]);
+            for (int lx = 0; lx < 2; ++lx) {
+                a.magic_wide[ly][lx] = magic(a.full_nd[ly] * a.n_wide[lx]);
+                a.magic_narrow[ly][lx] = magic(a.full_nd[ly] * a.n_narrow[lx]);
+            }
+        }
     }
 
     // Threads: whole multiples of 4 warps so that every scheduler of the SM gets the same number of warps

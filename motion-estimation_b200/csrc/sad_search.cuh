@@ -72,6 +72,9 @@ struct SearchArgs {
     // Index 0 = regular slab, 1 = last slab in x.
     int n_wide[2], n_narrow[2];
     unsigned short group[2][kMaxGroups];   // (s << 12) | q0
+    // fastdiv magics for the common case (a slab whose dy groups are all in the domain), [last slab in y][last slab in x]
+    int full_nd[2];
+    unsigned magic_nd[2], magic_wide[2][2], magic_narrow[2][2];
     // cross-slab argmin (only when nsx*nsy > 1): all-ones on entry, restored by the finalizing CTA
     unsigned long long *blk_key;   // [P][nb]
     unsigned int *tile_ticket;     // [P][tiles_per_pair] zero on entry, reset by the finalizing CTA
@@ -620,14 +623,17 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
         __syncthreads();
     }
 
-    // ---- candidate patches
-    const unsigned magic_nd = fastdiv_magic((unsigned)nd);
+    // ---- candidate patches.  The magic numbers of the usual case come precomputed from the host: a
+    //      64-bit division per warp and CTA showed up as 10 ALU instructions per work item in r01c.
+    const int lasty = sy == a.nsy - 1;
+    const bool usual = nd == a.full_nd[lasty];
+    const unsigned magic_nd = usual ? a.magic_nd[lasty] : fastdiv_magic((unsigned)nd);
     const unsigned short *grp = a.group[lastx];
     const int n_wide = a.n_wide[lastx], n_narrow = a.n_narrow[lastx];
     if (nd > 0) {   // wide patches: NDY x NQ
         const int per_j = nd * n_wide;
         const int total = nj * per_j;
-        const unsigned magic_pj = fastdiv_magic((unsigned)per_j);
+        const unsigned magic_pj = usual ? a.magic_wide[lasty][lastx] : fastdiv_magic((unsigned)per_j);
         const int iters = (total + (int)blockDim.x - 1) / (int)blockDim.x;
         for (int it = 0; it < iters; ++it) {
             const int w_raw = it * (int)blockDim.x + tid;
@@ -643,10 +649,11 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     if (nd > 0 && n_narrow > 0) {   // leftover columns: NDY x 1
         const int per_j = nd * n_narrow;
         const int total = nj * per_j;
-        const unsigned magic_pj = fastdiv_magic((unsigned)per_j);
+        const unsigned magic_pj = usual ? a.magic_narrow[lasty][lastx] : fastdiv_magic((unsigned)per_j);
         const int iters = (total + (int)blockDim.x - 1) / (int)blockDim.x;
         for (int it = 0; it < iters; ++it) {
-            const int w_raw = it * (int)blockDim.x + tid;
+            // handed out from the LAST warp down: the first warps carry the extra wide pass of a ragged tile
+            const int w_raw = it * (int)blockDim.x + ((int)blockDim.x - 1 - tid);
             const bool active = w_raw < total;
             const int w = active ? w_raw : total - 1;
             const int j = fastdiv(w, magic_pj), r = w - j * per_j;
