@@ -227,7 +227,8 @@ int configure(me_ctx *c)
                     p.nsx = nsx; p.nsy = nsy; p.su = su; p.sd = sd; p.pitch = pitch; p.tmb = t;
                     p.box_rows = box_rows; p.n_row_boxes = n_row_boxes;
                     p.copy = round_up(alloc_rows * pitch, 128);
-                    p.smem = a.n_bufs * p.copy + 256 + me::kRefPitch * B + me::kMaxKeys * 8 + 64;
+                    p.smem = a.n_bufs * p.copy + 128 + 256 + me::kRefPitch * B + me::kMaxKeys * 8 + 64;
+                    if (p.smem < 20 * 1024) p.smem = 20 * 1024;          // the pair reduction's histograms live in the same memory
                     if (p.smem > 227 * 1024) continue;
                     p.under = p.smem <= smem_cap;
                     p.work = (long long)t * NSUB * wmax * hmax;
@@ -269,22 +270,32 @@ int configure(me_ctx *c)
         const int w = t == 0 ? (a.nsx > 1 ? a.su : U) : U - (a.nsx - 1) * a.su;
         int ng = 0;
         a.n_wide[t] = a.n_narrow[t] = 0;
-        for (int pass = 0; pass < 2; ++pass)
-            for (int s = 0; s < 4; ++s) {
-                const int nq = (w - 1 - s) >= 0 ? (w - 1 - s) / 4 + 1 : 0;
-                const int nwide = nq / NQ;
-                if (pass == 0) {
-                    for (int g = 0; g < nwide; ++g, ++ng, ++a.n_wide[t]) {
-                        if (ng >= me::kMaxGroups) return fail(ME_EUNSUPPORTED, "range %d needs more than %d column groups", R, me::kMaxGroups);
-                        a.group[t][ng] = (unsigned short)((s << 12) | (g * NQ));
-                    }
-                } else {
-                    for (int q = nwide * NQ; q < nq; ++q, ++ng, ++a.n_narrow[t]) {
-                        if (ng >= me::kMaxGroups) return fail(ME_EUNSUPPORTED, "range %d needs more than %d column groups", R, me::kMaxGroups);
-                        a.group[t][ng] = (unsigned short)((s << 12) | q);
-                    }
+        // Order: group index major, shift minor.  Consecutive lanes then take the four shifted copies of
+        // two adjacent 16-byte column chunks; with the copies skewed 32 bytes apart (kCopySkew) the eight
+        // lanes of a quarter-warp hit eight different bank groups.  Lanes walk the column groups fastest, so
+        // the one padded dy group of a slab (U is rarely a multiple of NDY) stays in the last warp or two
+        // and every other warp takes the fast, test-free argmin path.
+        int nqs[4], nws[4], maxw = 0, maxn = 0;
+        for (int s = 0; s < 4; ++s) {
+            nqs[s] = (w - 1 - s) >= 0 ? (w - 1 - s) / 4 + 1 : 0;
+            nws[s] = nqs[s] / NQ;
+            if (nws[s] > maxw) maxw = nws[s];
+            if (nqs[s] - nws[s] * NQ > maxn) maxn = nqs[s] - nws[s] * NQ;
+        }
+        for (int g = 0; g < maxw; ++g)
+            for (int s = 0; s < 4; ++s)
+                if (g < nws[s]) {
+                    if (ng >= me::kMaxGroups) return fail(ME_EUNSUPPORTED, "range %d needs more than %d column groups", R, me::kMaxGroups);
+                    a.group[t][ng++] = (unsigned short)((s << 12) | (g * NQ));
+                    ++a.n_wide[t];
                 }
-            }
+        for (int k = 0; k < maxn; ++k)
+            for (int s = 0; s < 4; ++s)
+                if (nws[s] * NQ + k < nqs[s]) {
+                    if (ng >= me::kMaxGroups) return fail(ME_EUNSUPPORTED, "range %d needs more than %d column groups", R, me::kMaxGroups);
+                    a.group[t][ng++] = (unsigned short)((s << 12) | (nws[s] * NQ + k));
+                    ++a.n_narrow[t];
+                }
     }
 
     {   // fastdiv magics of full slabs (see sad_search.cuh)
@@ -298,6 +309,7 @@ int configure(me_ctx *c)
                 a.magic_narrow[ly][lx] = magic(a.full_nd[ly] * a.n_narrow[lx]);
             }
         }
+        for (int lx = 0; lx < 2; ++lx) { a.magic_nw[lx] = magic(a.n_wide[lx]); a.magic_nn[lx] = magic(a.n_narrow[lx]); }
     }
 
     // Threads: whole multiples of 4 warps so that every scheduler of the SM gets the same number of warps

@@ -38,6 +38,7 @@ constexpr int kMaxKeys = 32;          // blocks per tile
 constexpr int kMaxGroups = 96;        // column groups per block (wide + narrow)
 constexpr int kRefPitch = 256;        // bytes per row of the reference strip in shared memory
 constexpr unsigned kFull = 0xffffffffu;
+constexpr int kCopySkew = 32;         // copy s starts s*32 bytes further into the banks (see run_item lane mapping)
 
 // Compile-time geometry of a block size.
 template <int B> struct Geo {
@@ -75,6 +76,7 @@ struct SearchArgs {
     // fastdiv magics for the common case (a slab whose dy groups are all in the domain), [last slab in y][last slab in x]
     int full_nd[2];
     unsigned magic_nd[2], magic_wide[2][2], magic_narrow[2][2];
+    unsigned magic_nw[2], magic_nn[2];   // fastdiv by n_wide / n_narrow, [last slab in x]
     // cross-slab argmin (only when nsx*nsy > 1): all-ones on entry, restored by the finalizing CTA
     unsigned long long *blk_key;   // [P][nb]
     unsigned int *tile_ticket;     // [P][tiles_per_pair] zero on entry, reset by the finalizing CTA
@@ -293,104 +295,127 @@ __device__ __forceinline__ void finalize_block(const SearchArgs &a, int pair, co
 }
 
 // ---------------------------------------------------------------- per-pair median (last CTA)
-// k-th smallest key (0-based) among the axis' valid blocks by 4x8-bit MSB-first radix select.
-// Returns the key; *n_equal / *idx_in_equal describe the run of equal keys it sits in.
-__device__ uint32_t radix_select(const SearchArgs &a, int pair, int axis, unsigned need, unsigned k,
-                                 unsigned *hist, unsigned *bc, unsigned *n_equal, unsigned *idx_in_equal)
+// The CTA that takes the pair's last ticket reduces it while the rest of the grid works on other
+// pairs -- except for the last pair of a launch, where this code IS the tail of the launch (r01: 2.8 ms
+// of a 4.7 ms 4K launch in its first form: 11 passes with one dependent load chain per thread).
+// Now: an exact 3-level radix select (11 + 11 + 10 bits of the order-preserving float key), both axes
+// in the same pass, eight independent block records in flight per thread.  The level-0 histogram
+// also yields the counts, so the whole reduction is three streaming passes over the pair's records
+// (plus one when an even count needs the next larger key).
+constexpr uint32_t kNoKey = 0u;        // fkey() of a finite float is never 0
+constexpr int kSelBins = 2048;         // 11 bits per level; 2 axes x 2048 x 4 B = 16 KB of the CTA's shared memory
+constexpr int kSelUnroll = 8;
+
+__device__ __forceinline__ void pair_keys(const uint8_t *fl, const float2 *sub, int b, uint32_t &kx, uint32_t &ky)
 {
+    const unsigned f = __ldcg(fl + b);
+    const float2 v = __ldcg(sub + b);
+    kx = (f & (ME_FLAG_TEXTURED | ME_FLAG_X_PEAKED)) == (ME_FLAG_TEXTURED | ME_FLAG_X_PEAKED) ? fkey(v.x) : kNoKey;
+    ky = (f & (ME_FLAG_TEXTURED | ME_FLAG_Y_PEAKED)) == (ME_FLAG_TEXTURED | ME_FLAG_Y_PEAKED) ? fkey(v.y) : kNoKey;
+}
+
+// scratch: the CTA's shared memory from offset 0 (at least 2*kSelBins*4 + 128 bytes)
+__device__ void reduce_pair(const SearchArgs &a, int pair, unsigned *scratch)
+{
+    unsigned *hist = scratch;                    // [2][kSelBins]
+    unsigned *bc = scratch + 2 * kSelBins;       // per axis: [0] chosen bin, [1] rank inside it, [2] its count, [3] total
     const uint8_t *fl = a.blk_flags + (size_t)pair * a.nb;
-    const float *sub = a.blk_sub + (size_t)pair * a.nb * 2 + axis;
-    uint32_t prefix = 0, mask = 0;
-    for (int shift = 24; shift >= 0; shift -= 8) {
-        for (int i = threadIdx.x; i < 256; i += blockDim.x) hist[i] = 0;
+    const float2 *sub = reinterpret_cast<const float2 *>(a.blk_sub) + (size_t)pair * a.nb;
+    const int T = blockDim.x, tid = threadIdx.x;
+    uint32_t prefix[2] = {0, 0}, mask[2] = {0, 0};
+    unsigned k[2] = {0, 0}, cnt[2] = {0, 0}, neq[2] = {0, 0}, idx[2] = {0, 0};
+    bool even[2] = {false, false};
+    for (int level = 0; level < 3; ++level) {
+        const int shift = level == 0 ? 21 : level == 1 ? 10 : 0;
+        const uint32_t bmask = level == 2 ? 1023u : 2047u;
+        for (int i = tid; i < 2 * kSelBins; i += T) hist[i] = 0;
         __syncthreads();
-        for (int b = threadIdx.x; b < a.nb; b += blockDim.x) {
-            if ((__ldcg(fl + b) & need) == need) {
-                const uint32_t key = fkey(__ldcg(sub + 2 * b));
-                if ((key & mask) == prefix) atomicAdd(&hist[(key >> shift) & 255u], 1u);
+        for (int b0 = tid; b0 < a.nb; b0 += kSelUnroll * T) {
+            uint32_t kx[kSelUnroll], ky[kSelUnroll];
+#pragma unroll
+            for (int u = 0; u < kSelUnroll; ++u) {
+                kx[u] = ky[u] = kNoKey;
+                if (b0 + u * T < a.nb) pair_keys(fl, sub, b0 + u * T, kx[u], ky[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < kSelUnroll; ++u) {
+                if (kx[u] != kNoKey && (kx[u] & mask[0]) == prefix[0]) atomicAdd(&hist[(kx[u] >> shift) & bmask], 1u);
+                if (ky[u] != kNoKey && (ky[u] & mask[1]) == prefix[1]) atomicAdd(&hist[kSelBins + ((ky[u] >> shift) & bmask)], 1u);
             }
         }
         __syncthreads();
-        if (threadIdx.x < 32) {                     // warp 0: find the bin holding rank k
-            const int lane = threadIdx.x;
+        if (tid < 64) {                              // warp 0: x axis, warp 1: y axis
+            const int axis = tid >> 5, lane = tid & 31;
+            const unsigned *h = hist + axis * kSelBins;
+            constexpr int per = kSelBins / 32;
             unsigned mine = 0;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) mine += hist[lane * 8 + i];
+            for (int i = 0; i < per; ++i) mine += h[lane * per + i];
             unsigned incl = mine;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
-                unsigned t = __shfl_up_sync(kFull, incl, o);
+                const unsigned t = __shfl_up_sync(kFull, incl, o);
                 if (lane >= o) incl += t;
             }
+            const unsigned total = __shfl_sync(kFull, incl, 31);
+            unsigned kk = k[axis];
+            if (level == 0) kk = total ? (total - 1) / 2 : 0;       // lower middle of this axis
             const unsigned excl = incl - mine;
-            const bool has = k >= excl && k < incl;   // exactly one lane
-            if (has) {
+            if (lane == 0) { bc[axis * 4 + 3] = total; if (total == 0) { bc[axis * 4] = 0; bc[axis * 4 + 1] = 0; bc[axis * 4 + 2] = 0; } }
+            if (total && kk >= excl && kk < incl) {                 // exactly one lane
                 unsigned cum = excl;
-                int sel = 0;
-                for (int i = 0; i < 8; ++i) {
-                    const unsigned h = hist[lane * 8 + i];
-                    if (k < cum + h) { sel = lane * 8 + i; break; }
-                    cum += h;
+                int sel = lane * per;
+                for (int i = 0; i < per; ++i) {
+                    const unsigned c = h[lane * per + i];
+                    if (kk < cum + c) { sel = lane * per + i; break; }
+                    cum += c;
                 }
-                bc[0] = (unsigned)sel;
-                bc[1] = k - cum;                    // rank inside the chosen bin
-                bc[2] = hist[sel];
+                bc[axis * 4] = (unsigned)sel;
+                bc[axis * 4 + 1] = kk - cum;
+                bc[axis * 4 + 2] = h[sel];
             }
         }
         __syncthreads();
-        prefix |= bc[0] << shift;
-        mask |= 255u << shift;
-        k = bc[1];
-        if (shift == 0) { *n_equal = bc[2]; *idx_in_equal = bc[1]; }
-        __syncthreads();
-    }
-    return prefix;
-}
-
-__device__ void reduce_pair(const SearchArgs &a, int pair, unsigned *scratch)
-{
-    unsigned *hist = scratch;          // 256
-    unsigned *bc = scratch + 256;      // broadcast slots
-    const uint8_t *fl = a.blk_flags + (size_t)pair * a.nb;
-    const float *sub = a.blk_sub + (size_t)pair * a.nb * 2;
-    float med[2];
-    unsigned cnt[2];
-    for (int axis = 0; axis < 2; ++axis) {
-        const unsigned need = ME_FLAG_TEXTURED | (axis ? ME_FLAG_Y_PEAKED : ME_FLAG_X_PEAKED);
-        if (threadIdx.x == 0) { bc[4] = 0; bc[5] = 0xffffffffu; }
-        __syncthreads();
-        unsigned local = 0;
-        for (int b = threadIdx.x; b < a.nb; b += blockDim.x) local += ((__ldcg(fl + b) & need) == need);
-        local = __reduce_add_sync(kFull, local);
-        if ((threadIdx.x & 31) == 0 && local) atomicAdd(&bc[4], local);
-        __syncthreads();
-        const unsigned n = bc[4];
-        cnt[axis] = n;
-        med[axis] = 0.0f;
-        if (n == 0) { __syncthreads(); continue; }   // uniform across the CTA
-        const unsigned k1 = (n - 1) / 2, k2 = n / 2;
-        unsigned neq = 0, idx = 0;
-        const uint32_t v1 = radix_select(a, pair, axis, need, k1, hist, bc, &neq, &idx);
-        uint32_t v2 = v1;
-        if (k2 != k1 && idx + 1 >= neq) {           // upper middle is the next larger key
-            uint32_t best = 0xffffffffu;
-            for (int b = threadIdx.x; b < a.nb; b += blockDim.x)
-                if ((__ldcg(fl + b) & need) == need) {
-                    const uint32_t key = fkey(__ldcg(sub + 2 * b + axis));
-                    if (key > v1 && key < best) best = key;
-                }
-            best = __reduce_min_sync(kFull, best);
-            if ((threadIdx.x & 31) == 0) atomicMin(&bc[5], best);
-            __syncthreads();
-            v2 = bc[5];
+#pragma unroll
+        for (int axis = 0; axis < 2; ++axis) {
+            if (level == 0) { cnt[axis] = bc[axis * 4 + 3]; even[axis] = cnt[axis] && (cnt[axis] & 1u) == 0; }
+            prefix[axis] |= bc[axis * 4] << shift;
+            mask[axis] |= bmask << shift;
+            k[axis] = bc[axis * 4 + 1];
+            if (level == 2) { neq[axis] = bc[axis * 4 + 2]; idx[axis] = bc[axis * 4 + 1]; }
         }
-        med[axis] = __fmul_rn(0.5f, __fadd_rn(funkey(v1), funkey(v2)));
         __syncthreads();
     }
-    if (threadIdx.x == 0) {
+    // upper middle: the same key unless the lower middle is the last of its run and the count is even
+    uint32_t v2[2] = {prefix[0], prefix[1]};
+    const bool need0 = even[0] && idx[0] + 1 >= neq[0], need1 = even[1] && idx[1] + 1 >= neq[1];
+    if (need0 || need1) {                            // uniform across the CTA
+        if (tid == 0) { bc[8] = 0xffffffffu; bc[9] = 0xffffffffu; }
+        __syncthreads();
+        uint32_t bx = 0xffffffffu, by = 0xffffffffu;
+        for (int b0 = tid; b0 < a.nb; b0 += kSelUnroll * T) {
+            uint32_t kx[kSelUnroll], ky[kSelUnroll];
+#pragma unroll
+            for (int u = 0; u < kSelUnroll; ++u) {
+                kx[u] = ky[u] = kNoKey;
+                if (b0 + u * T < a.nb) pair_keys(fl, sub, b0 + u * T, kx[u], ky[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < kSelUnroll; ++u) {
+                if (kx[u] != kNoKey && kx[u] > prefix[0] && kx[u] < bx) bx = kx[u];
+                if (ky[u] != kNoKey && ky[u] > prefix[1] && ky[u] < by) by = ky[u];
+            }
+        }
+        bx = __reduce_min_sync(kFull, bx);
+        by = __reduce_min_sync(kFull, by);
+        if ((tid & 31) == 0) { atomicMin(&bc[8], bx); atomicMin(&bc[9], by); }
+        __syncthreads();
+        if (need0) v2[0] = bc[8];
+        if (need1) v2[1] = bc[9];
+    }
+    if (tid == 0) {
         me_pair_result r;
-        r.pdx = med[0];
-        r.pdy = med[1];
+        r.pdx = cnt[0] ? __fmul_rn(0.5f, __fadd_rn(funkey(prefix[0]), funkey(v2[0]))) : 0.0f;
+        r.pdy = cnt[1] ? __fmul_rn(0.5f, __fadd_rn(funkey(prefix[1]), funkey(v2[1]))) : 0.0f;
         r.flag = (int)cnt[0] >= (a.min_valid > 1 ? a.min_valid : 1);
         r.nvalid_x = (int)cnt[0];
         r.nvalid_y = (int)cnt[1];
@@ -427,7 +452,7 @@ __device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j
             for (int d = 0; d < NDY; ++d)
 #pragma unroll
                 for (int q = 0; q < NQP; ++q) acc[sb][d][q] = 0;
-        const uint32_t *cur = reinterpret_cast<const uint32_t *>(s_win + (size_t)s * a.copy_bytes) +
+        const uint32_t *cur = reinterpret_cast<const uint32_t *>(s_win + (size_t)s * (a.copy_bytes + kCopySkew)) +
                               dyg * NDY * (PITCH / 4) + j * G::BW + q0;
         const uint32_t *ref = reinterpret_cast<const uint32_t *>(s_ref) + j * G::BW;
         sad_patch<B, NDY, NQP, PITCH, LW>(cur, ref, acc);
@@ -524,8 +549,8 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     const int nblk = min(nj * G::NSUB, a.nbx - tx * a.tmb * G::NSUB);  // blocks in this tile
 
     uint8_t *s_win = smem;                                            // 4 shifted copies
-    uint8_t *s_raw = a.x_off ? smem + 4 * (size_t)a.copy_bytes : smem; // TMA destination
-    uint8_t *s_ref = smem + (size_t)a.n_bufs * a.copy_bytes + 256;    // 256 B of slack for tile over-reads
+    uint8_t *s_raw = a.x_off ? smem + 4 * (size_t)a.copy_bytes + 128 : smem;   // TMA destination (128-byte aligned)
+    uint8_t *s_ref = smem + (size_t)a.n_bufs * a.copy_bytes + 128 + 256;       // copy skews + 256 B of slack for tile over-reads
     constexpr int ref_bytes = kRefPitch * B;
     KeyT *s_key = reinterpret_cast<KeyT *>(s_ref + ref_bytes);         // [kMaxKeys]
     uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_ref + ref_bytes + kMaxKeys * 8);
@@ -593,7 +618,7 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
                     o.y = __funnelshift_r(v.y, v.z, 8 * s);
                     o.z = __funnelshift_r(v.z, v.w, 8 * s);
                     o.w = __funnelshift_r(v.w, w4, 8 * s);
-                    *reinterpret_cast<uint4 *>(s_win + (size_t)s * a.copy_bytes + 16 * (size_t)i) = o;
+                    *reinterpret_cast<uint4 *>(s_win + (size_t)s * (a.copy_bytes + kCopySkew) + 16 * (size_t)i) = o;
                 }
             }
         } else {
@@ -616,7 +641,7 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
                     o.y = __funnelshift_r(e[1], e[2], bits);
                     o.z = __funnelshift_r(e[2], e[3], bits);
                     o.w = __funnelshift_r(e[3], e[4], bits);
-                    *reinterpret_cast<uint4 *>(s_win + (size_t)s * a.copy_bytes + 16 * (size_t)i) = o;
+                    *reinterpret_cast<uint4 *>(s_win + (size_t)s * (a.copy_bytes + kCopySkew) + 16 * (size_t)i) = o;
                 }
             }
         }
@@ -627,7 +652,6 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     //      64-bit division per warp and CTA showed up as 10 ALU instructions per work item in r01c.
     const int lasty = sy == a.nsy - 1;
     const bool usual = nd == a.full_nd[lasty];
-    const unsigned magic_nd = usual ? a.magic_nd[lasty] : fastdiv_magic((unsigned)nd);
     const unsigned short *grp = a.group[lastx];
     const int n_wide = a.n_wide[lastx], n_narrow = a.n_narrow[lastx];
     if (nd > 0) {   // wide patches: NDY x NQ
@@ -640,7 +664,7 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
             const bool active = w_raw < total;
             const int w = active ? w_raw : total - 1;
             const int j = fastdiv(w, magic_pj), r = w - j * per_j;
-            const int cg = fastdiv(r, magic_nd), dyg = dyg_lo + r - cg * nd;   // dy group varies fastest across lanes
+            const int dq = fastdiv(r, a.magic_nw[lastx]), cg = r - dq * n_wide, dyg = dyg_lo + dq;   // column group varies fastest across lanes
             const unsigned g = grp[cg];
             run_item<B, NDY, NQ, PITCH, LWW, K64, RB>(a, active, j, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
                                                       s_key, tile_interior, dyi_lo, dyi_hi, X0, lane, ubase, dbase, slab_w);
@@ -657,7 +681,7 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
             const bool active = w_raw < total;
             const int w = active ? w_raw : total - 1;
             const int j = fastdiv(w, magic_pj), r = w - j * per_j;
-            const int cg = fastdiv(r, magic_nd), dyg = dyg_lo + r - cg * nd;
+            const int dq = fastdiv(r, a.magic_nn[lastx]), cg = r - dq * n_narrow, dyg = dyg_lo + dq;
             const unsigned g = grp[n_wide + cg];
             run_item<B, NDY, 1, PITCH, 1, K64, RB>(a, active, j, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
                                                    s_key, tile_interior, dyi_lo, dyi_hi, X0, lane, ubase, dbase, slab_w);
@@ -712,7 +736,7 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     __syncthreads();
     if (*s_last) {
         __threadfence();
-        reduce_pair(a, pair, reinterpret_cast<unsigned *>(s_win));
+        reduce_pair(a, pair, reinterpret_cast<unsigned *>(smem));
     }
 }
 
