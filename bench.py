@@ -223,7 +223,7 @@ def run_ours(args):
     alg_bytes = (PAIRS + 1) * H * W + PAIRS * geo["nbx"] * geo["nby"] * 17 + PAIRS * 24
     hbm_gbs = float(peaks["hbm_gbs"])
     roofline = {
-        "bound": "int_alu", "kernel": "sad_search_kernel<16,5,4>", "achieved": achieved / 1e9, "peak": peak_alu / 1e9,
+        "bound": "int_alu", "kernel": f"sad_search_kernel<16,5,4,{geo['window_pitch']}>", "achieved": achieved / 1e9, "peak": peak_alu / 1e9,
         "unit": "Gcand*px/s", "frac": achieved / peak_alu, "traffic": traffic,
         "peak_is": f"{sms} SMs x {ipc:.2f} VABSDIFF4 thread-instr/clk/SM (microbenchmarked in this run) x 4 px x "
                    f"{f_max / 1e6:.0f} MHz max SM clock; {peak_src}",
@@ -256,6 +256,7 @@ def run_ours(args):
                    "l2": f"inputs larger than L2: {(PAIRS + 1) * H * W / 1e6:.1f} MB of frames per step vs 126 MB",
                    "parallelism": f"frame pairs sharded over {world} GPU(s), one all_gather of pair records per step",
                    "tile_blocks_x": geo["tile_blocks_x"], "threads_per_cta": geo["threads_per_cta"],
+                   "window_pitch": geo["window_pitch"], "candidate_slabs": [geo["slabs_x"], geo["slabs_y"]],
                    "smem_bytes": geo["smem_bytes"], "ctas_per_pair": geo["tiles_per_pair"]},
         "gcand_px_per_s": achieved / 1e9,
         "clocks": clocks,

@@ -54,7 +54,7 @@ typedef struct me_ctx me_ctx;
  * estimate_vel_vid.py:308-309); they are the knobs of the block search that replaces it. */
 typedef struct me_params {
     int32_t block;      /* B: 8, 16 or 32                                                     */
-    int32_t range;      /* R: 1 .. 127 (larger ranges are cut into slabs, one CTA each)       */
+    int32_t range;      /* R: 1 .. 128 (large ranges are cut into slabs, one CTA each)        */
     int32_t min_range;  /* texture gate: block max-min >= min_range grey levels               */
     int32_t subpixel;   /* 0 = integer displacements only                                     */
     int32_t min_valid;  /* pair flag = nvalid_x >= max(min_valid, 1)                          */

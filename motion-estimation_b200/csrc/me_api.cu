@@ -95,8 +95,8 @@ template <int PITCH>
 KernelChoice pick_pitch(int B, bool k64)
 {
     switch (B) {
-    case 8:  return choice<8, PITCH, false, 16>();      // sad < 2^14, rank < 2^16
-    case 16: return choice<16, PITCH, false, 16>();     // sad < 2^16, rank < 2^16
+    case 8:  return k64 ? choice<8, PITCH, true, 32>() : choice<8, PITCH, false, 16>();     // sad < 2^14; rank < 2^16 unless R = 128
+    case 16: return k64 ? choice<16, PITCH, true, 32>() : choice<16, PITCH, false, 16>();   // sad < 2^16
     default: return k64 ? choice<32, PITCH, true, 32>() : choice<32, PITCH, false, 14>();   // sad < 2^18
     }
 }
@@ -171,8 +171,8 @@ int configure(me_ctx *c)
     a.min_range = c->p.min_range; a.min_curv = c->p.min_curv; a.subpixel = c->p.subpixel; a.min_valid = c->p.min_valid;
 
     // key width: (sad << RB) | rank must fit; 32-bit keys use RB = 16 (B <= 16) or 14 (B = 32)
-    if (U > 255) return fail(ME_EUNSUPPORTED, "range %d: the candidate rank needs more than 16 bits (range <= 127)", R);
-    const bool k64 = B == 32 && (long long)U * U > (1ll << 14);
+    if (R > 128) return fail(ME_EUNSUPPORTED, "range %d: ranges up to 128 are built", R);
+    const bool k64 = (long long)U * U > (B == 32 ? (1ll << 14) : (1ll << 16));   // R = 128 needs a 17-bit rank
 
     // TMA needs a 16-byte aligned x origin; tiles and slabs start at multiples of 16, so the slack is fixed.
     a.x_off = (16 - R % 16) % 16;

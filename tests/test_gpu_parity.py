@@ -34,6 +34,7 @@ CASES = [
     (270, 480, 16, 32), (136, 256, 8, 64), (48, 64, 16, 1), (33, 47, 16, 5), (64, 128, 32, 40),
     (80, 144, 16, 50), (16, 16, 16, 4), (40, 336, 8, 7), (128, 128, 16, 96),
     (160, 192, 16, 100), (144, 304, 16, 127), (72, 136, 8, 90), (200, 168, 32, 72),   # ranges that need candidate slabs
+    (144, 320, 16, 128), (80, 304, 8, 128),                                          # 17-bit candidate rank: 64-bit keys
 ]
 
 
@@ -190,8 +191,8 @@ def test_errors_are_reported_not_swallowed(me):
         with pytest.raises(ValueError):
             est.upload(np.zeros((1, 32, 128), np.uint8))    # wrong frame height
     with pytest.raises(me.MEError) as e:
-        me.MotionEstimator(64, 128, me.SearchConfig(16, 128))
-    assert e.value.code == -2 and "range" in str(e.value)   # candidate rank is 16 bits: range <= 127
+        me.MotionEstimator(64, 128, me.SearchConfig(16, 129))
+    assert e.value.code == -2 and "range" in str(e.value)   # ranges up to 128 are built
 
 
 # ----------------------------------------------------------------------------- BASELINE sizes
