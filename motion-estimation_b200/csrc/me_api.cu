@@ -184,7 +184,8 @@ int configure(me_ctx *c)
     // list of odd multiples of 16 bytes: with NDY = 5 the 8 lanes of a quarter-warp, which read rows
     // NDY apart, then land in 8 different 16-byte bank groups (r01 ncu: a 256-byte pitch cost 5.4
     // wavefronts per LDS.128 and made the kernel shared-memory bound).
-    const int smem_cap = env_int("ME_SMEM_CAP", 72 * 1024);
+    // 3 CTAs per SM for 8/16-pixel blocks; 32-pixel blocks do better with two larger tiles per SM (r01 sweep: 0.74 vs 0.50)
+    const int smem_cap = env_int("ME_SMEM_CAP", B == 32 ? 110 * 1024 : 72 * 1024);
     const int forced_tmb = env_int("ME_TBX", 0), forced_pitch = env_int("ME_PITCH", 0);
     const int forced_nsx = env_int("ME_NSX", 0), forced_nsy = env_int("ME_NSY", 0);
     const long long work_enough = 32000;          // block-candidates per CTA beyond which a bigger CTA buys nothing
@@ -315,7 +316,7 @@ int configure(me_ctx *c)
     // Threads: whole multiples of 4 warps so that every scheduler of the SM gets the same number of warps
     // (r01 sweep: 224 threads = 7 warps ran 13 % slower than 128 or 256).
     const int total = a.tmb * ceil_div(U - (a.nsy - 1) * a.sd, NDY) * a.n_wide[1];
-    c->threads = env_int("ME_THREADS", total >= 512 ? 256 : 128);
+    c->threads = env_int("ME_THREADS", total >= 384 ? 256 : 128);
     if (c->threads % 32 || c->threads < 32 || c->threads > c->kc.maxt)
         return fail(ME_EINVAL, "ME_THREADS=%d is not a multiple of 32 in [32,%d]", c->threads, c->kc.maxt);
     a.use_tma = env_int("ME_NO_TMA", 0) ? 0 : 1;
