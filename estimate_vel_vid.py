@@ -13,7 +13,6 @@ decoded sequentially into one array.  CLAHE / non-local-means pre-processing (re
 201-299, 99 % of its run time) is outside this path and is not applied unless --clahe is given.
 """
 import argparse
-import csv
 import os
 import sys
 from pathlib import Path
@@ -78,10 +77,16 @@ def main(argv=None):
                           device=a.device, units=a.units, return_details=True)
     out_dir = str(a.out) if a.out else (src if os.access(src, os.W_OK) else os.getcwd())
     os.makedirs(out_dir, exist_ok=True)
-    with open(os.path.join(out_dir, "velocity_estimates.csv"), "w", newline="") as f:
-        w = csv.writer(f)
-        w.writerow(["Timestamp [s]", "mm/min X-axis optical", "mm/min Y-axis optical"])   # header order as in the reference
-        w.writerows(res.out_information)                                                   # rows are (vx, vy, t), also as there
+    from motion_estimation_b200 import postprocess
+    postprocess.write_velocity_csv(out_dir, res.out_information)        # reference header + (vx, vy, t) rows (its lines 410, 572)
+    # encoder ground truth and the resampled position series, when the recording ships an encoder log (reference 417-487, 589-642)
+    import glob
+    if glob.glob(os.path.join(src, "*encoder.csv")) and len(res.tsList) >= 3:
+        last_line = first + len(frames)
+        enc_pos, enc_ts = postprocess.encoder_velocity(src, last_line)
+        opt, enc, grid, _, _ = postprocess.dataset_correlation(res.motion_list_opt, res.tsList, enc_pos, enc_ts)
+        postprocess.write_positions_csv(out_dir, grid, opt, enc)
+        print(f"wrote {os.path.join(out_dir, 'correlated_positions.csv')}")
     pos = res.motion_list_opt[-1] if res.motion_list_opt else 0.0
     print(f"\nfailed motion estimates: {res.failed_estimates} of {len(number_list)}")
     print(f"final position according to block search: {pos}")

@@ -67,6 +67,30 @@ def decode(directory, first, n):
     return np.stack(frames)
 
 
+def encoder_golden():
+    """Trimmed copy of the 116.4 recording's encoder log + timecodes (data, not code) as a fixture
+    directory, and what the reference's encoder_velocity / dataset_correlation return on it."""
+    from scipy import interpolate
+    src_dir = os.path.join(REF, "examples/116.4_mm_min.d")
+    fix = os.path.join(OUT, "encoder_116.4")
+    os.makedirs(fix, exist_ok=True)
+    enc = open(glob.glob(os.path.join(src_dir, "*encoder.csv"))[0]).read().split("\n")[:9000]
+    open(os.path.join(fix, "excerpt_encoder.csv"), "w").write("\n".join(enc) + "\n")
+    ts = open(glob.glob(os.path.join(src_dir, "*tstamps.txt"))[0]).read().split("\n")[:700]
+    open(os.path.join(fix, "excerpt_tstamps.txt"), "w").write("\n".join(ts) + "\n")
+    last_frame = 600
+    ns = reference_functions({"encoder_velocity", "dataset_correlation", "encoder_out_info_list", "enc_pos_list", "enc_ts_list"},
+                             {"imagePath": fix, "lastFrame": last_frame, "interpolate": interpolate})
+    pos, t = ns["encoder_velocity"]()
+    opt_t = list(np.linspace(0.01, t[-1] * 0.9, 40))
+    opt_p = list(np.cumsum(np.linspace(0.05, 0.3, 40)))
+    r = ns["dataset_correlation"](opt_p, opt_t, pos, t)
+    np.savez_compressed(os.path.join(OUT, "encoder_116.4.npz"), last_frame=last_frame, enc_pos=np.array(pos), enc_ts=np.array(t),
+                        opt_t=np.array(opt_t), opt_p=np.array(opt_p), corr_opt=np.asarray(r[0], float), corr_enc=np.asarray(r[1], float),
+                        corr_grid=np.asarray(r[2], float), corr_vel_enc=np.asarray(r[3], float), corr_vel_opt=np.asarray(r[4], float))
+    return dict(rows=len(pos), last_frame=last_frame)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ref = reference_functions({"calc_ECC_transform", "calculate_dense_flow", "FB_opt_flow_params"}, {})
@@ -121,6 +145,7 @@ def main():
                              ecc_flags=[int(v) for v in ecc_ref[:, 2]], endproc_rows=len(out_information),
                              cv2=cv.__version__)
         print(name, summary[name])
+    summary["encoder"] = encoder_golden()
     with open(os.path.join(OUT, "MANIFEST.json"), "w") as f:
         json.dump(dict(generated_by="tools/make_golden.py", reference="/root/reference (ruzko/motion-estimation)",
                        clips=summary), f, indent=1)
