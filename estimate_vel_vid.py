@@ -82,7 +82,10 @@ def main(argv=None):
     # encoder ground truth and the resampled position series, when the recording ships an encoder log (reference 417-487, 589-642)
     import glob
     if glob.glob(os.path.join(src, "*encoder.csv")) and len(res.tsList) >= 3:
-        last_line = first + len(frames)
+        # the reference indexes the timecode file with lastFrame (its line 429); the example files are
+        # truncated, so fall back to the last line that still holds a value
+        stamp_lines = open(ingest.find_timestamps(src)).read().split("\n")
+        last_line = min(first + len(frames), max(i + 1 for i, v in enumerate(stamp_lines) if v.strip() and not v.startswith("#")))
         enc_pos, enc_ts = postprocess.encoder_velocity(src, last_line)
         opt, enc, grid, _, _ = postprocess.dataset_correlation(res.motion_list_opt, res.tsList, enc_pos, enc_ts)
         postprocess.write_positions_csv(out_dir, grid, opt, enc)
