@@ -36,7 +36,7 @@ def parse(argv=None):
                     help="'reference' halves displacements like the reference's half-resolution ECC result")
     ap.add_argument("--device", type=int, default=0)
     ap.add_argument("--out", type=Path, default=None, help="directory for the CSV (default: DIR, else the cwd)")
-    ap.add_argument("--clahe", action="store_true", help="apply cv.createCLAHE(2.0,(8,8)) per frame like reference :201-219")
+    ap.add_argument("--clahe", action="store_true", help="apply CLAHE(2.0,(8,8)) per frame like reference :201-219 (GPU kernels, bit-exact with cv2)")
     a = ap.parse_args(argv)
     whole = a.useWholeVideo == "True"
     if not whole and len(a.fileIndex) != 2:
@@ -64,11 +64,9 @@ def main(argv=None):
                 sys.exit(f"no *.h264 in {src}")
             target = str(hits[0])
         frames = ingest.read_frames(target, first, last)
-        if a.clahe:
-            import cv2 as cv
-            clahe = cv.createCLAHE(clipLimit=2.0, tileGridSize=(8, 8))
-            for i in range(len(frames)):
-                frames[i] = clahe.apply(frames[i])
+        if a.clahe:                                   # reference lines 201-219, on the GPU, bit-exact with cv2's CLAHE
+            api.set_defaults(device=a.device)
+            frames = api.adaptive_histogram_equalization(frames)
     if len(frames) < 2:
         sys.exit("need at least two frames")
     number_list = list(range(first, first + len(frames) + 1))

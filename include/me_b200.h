@@ -113,6 +113,16 @@ int me_upload(me_ctx *ctx, const uint8_t *luma, size_t row_pitch, int first_slot
  * the BGR2GRAY conversion runs on the GPU, bit-exact with cv.cvtColor's 15-bit fixed point. */
 int me_upload_bgr(me_ctx *ctx, const uint8_t *bgr, size_t row_pitch, int first_slot, int n_frames);
 
+/* Contrast-limited adaptive histogram equalisation of ring slots, in place, on the GPU -- replaces the
+ * per-frame cv.createCLAHE(clipLimit=2.0, tileGridSize=(8,8)).apply(z) of adaptive_histogram_equalization
+ * (estimate_vel_vid.py:201-219), bit-exact with OpenCV's 8-bit CLAHE.  Runs on the copy stream, after the
+ * uploads issued so far; later searches wait for it. */
+int me_clahe(me_ctx *ctx, int first_slot, int n_frames, double clip_limit, int tiles_x, int tiles_y);
+
+/* Copy ring slots back to host memory (row_pitch bytes between rows); waits for pending uploads and CLAHE.
+ * The reference keeps every stage's frames as (N,H,W) host arrays (estimate_vel_vid.py:215-219). */
+int me_download(me_ctx *ctx, uint8_t *luma, size_t row_pitch, int first_slot, int n_frames);
+
 /* Launch the search for n_pairs pairs of ring slots: pairs[2k] = previous frame, pairs[2k+1] =
  * current frame.  Asynchronous; results are read with me_fetch_*.  This is the call that replaces
  * the body of calc_ECC_transform for a whole batch. */

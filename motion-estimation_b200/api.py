@@ -118,6 +118,28 @@ def calculate_dense_flow(prevFrame, curFrame, *, config: Optional[SearchConfig] 
     return mx, my
 
 
+def adaptive_histogram_equalization(noisy_arrs, *, clip_limit: float = 2.0, tiles=(8, 8), device: Optional[int] = None,
+                                    chunk: int = 256):
+    """(N,H,W) uint8 -> CLAHE-equalised (N,H,W) uint8 -- estimate_vel_vid.py:201-219, on the GPU.
+
+    Same result as ``cv.createCLAHE(clipLimit=2.0, tileGridSize=(8,8)).apply`` per frame (bit-exact), written
+    into one preallocated array instead of the reference's per-frame ``np.append`` (:215)."""
+    frames = np.ascontiguousarray(noisy_arrs, dtype=np.uint8)
+    if frames.ndim != 3:
+        raise ValueError("noisy_arrs must be (N, H, W) uint8")
+    n = frames.shape[0]
+    chunk = max(1, min(chunk, n))
+    eng = _engine(frames.shape[1], frames.shape[2], default_config, default_device if device is None else device,
+                  max(chunk, 2), 1)
+    out = np.empty_like(frames)
+    for k in range(0, n, chunk):
+        m = min(chunk, n - k)
+        eng.upload(frames[k:k + m], first_slot=0)
+        eng.clahe(0, m, clip_limit, tiles)
+        out[k:k + m] = eng.download(0, m)
+    return out
+
+
 class _RingSource:
     """d(anchor, k) for a host frame stack through a bounded device ring.
 

@@ -14,6 +14,7 @@
 
 #include "../../include/me_b200.h"
 #include "sad_search.cuh"
+#include "clahe.cuh"
 
 namespace {
 
@@ -133,6 +134,8 @@ struct me_ctx {
     int stage_next = 0;
     uint8_t *d_bgr = nullptr;
     size_t d_bgr_bytes = 0;
+    uint8_t *d_luts = nullptr;          // CLAHE lookup tables, allocated on first use
+    size_t d_luts_bytes = 0;
     // streams / events
     cudaStream_t s_copy = nullptr, s_compute = nullptr;
     cudaEvent_t ev_upload = nullptr, ev_search = nullptr, ev_k0 = nullptr, ev_k1 = nullptr;
@@ -527,7 +530,7 @@ int me_destroy(me_ctx *c)
     cudaSetDevice(c->device);
     if (c->s_copy) cudaStreamSynchronize(c->s_copy);
     if (c->s_compute) cudaStreamSynchronize(c->s_compute);
-    cudaFree(c->d_frames); cudaFree(c->d_bgr); cudaFree(c->d_pairs);
+    cudaFree(c->d_frames); cudaFree(c->d_bgr); cudaFree(c->d_luts); cudaFree(c->d_pairs);
     cudaFree(c->args.blk_mv); cudaFree(c->args.blk_sad); cudaFree(c->args.blk_sub); cudaFree(c->args.blk_flags);
     cudaFree(c->args.pair_out); cudaFree(c->args.pair_ticket); cudaFree(c->args.blk_key); cudaFree(c->args.tile_ticket);
     for (int i = 0; i < 2; ++i) {
@@ -573,6 +576,60 @@ int me_upload_bgr(me_ctx *c, const uint8_t *bgr, size_t row_pitch, int first_slo
 {
     if (!c) return fail(ME_EINVAL, "ctx is NULL");
     return upload_impl(c, bgr, row_pitch, first_slot, n_frames, true);
+}
+
+int me_clahe(me_ctx *c, int first_slot, int n_frames, double clip_limit, int tiles_x, int tiles_y)
+{
+    if (!c) return fail(ME_EINVAL, "ctx is NULL");
+    if (n_frames < 1 || first_slot < 0 || first_slot + n_frames > c->max_frames)
+        return fail(ME_EINVAL, "%d frames at slot %d do not fit the %d-slot ring", n_frames, first_slot, c->max_frames);
+    if (tiles_x < 1 || tiles_y < 1 || tiles_x > 64 || tiles_y > 64 || clip_limit < 0)
+        return fail(ME_EINVAL, "tile grid %dx%d (1..64 each) / clip limit %g", tiles_x, tiles_y, clip_limit);
+    CU_TRY(cudaSetDevice(c->device));
+    me::ClaheArgs a;
+    a.frames = c->d_frames; a.frame_stride = (long long)c->frame_stride; a.pitch = (int)c->pitch; a.W = c->W; a.H = c->H;
+    a.tx = tiles_x; a.ty = tiles_y;
+    int We = c->W, He = c->H;
+    if (c->W % tiles_x || c->H % tiles_y) { We = c->W + tiles_x - c->W % tiles_x; He = c->H + tiles_y - c->H % tiles_y; }   // OpenCV's border rule
+    a.tw = We / tiles_x; a.th = He / tiles_y;
+    if (We - c->W >= c->W || He - c->H >= c->H) return fail(ME_EINVAL, "frame %dx%d too small for a %dx%d tile grid", c->W, c->H, tiles_x, tiles_y);
+    const int area = a.tw * a.th;
+    a.lut_scale = 255.0f / (float)area;
+    a.clip = 0;
+    if (clip_limit > 0) { a.clip = (int)(clip_limit * area / 256); if (a.clip < 1) a.clip = 1; }
+    a.inv_tw = 1.0f / (float)a.tw; a.inv_th = 1.0f / (float)a.th;
+    const size_t need = (size_t)c->max_frames * tiles_x * tiles_y * 256;
+    if (c->d_luts_bytes < need) {
+        CU_TRY(cudaStreamSynchronize(c->s_copy));
+        if (c->d_luts) CU_TRY(cudaFree(c->d_luts));
+        c->d_luts = nullptr; c->d_luts_bytes = 0;
+        CU_TRY(cudaMalloc(&c->d_luts, need));
+        c->d_luts_bytes = need;
+    }
+    a.luts = c->d_luts;
+    for (auto &r : c->recent)                        // the frames are rewritten in place: wait for searches that read them
+        if (r.used && r.lo < first_slot + n_frames && r.hi >= first_slot) CU_TRY(cudaStreamWaitEvent(c->s_copy, r.done, 0));
+    me::clahe_lut_kernel<<<dim3((unsigned)(tiles_x * tiles_y), (unsigned)n_frames), 256, 0, c->s_copy>>>(a, first_slot);
+    CU_TRY(cudaGetLastError());
+    me::clahe_apply_kernel<<<dim3((unsigned)ceil_div(ceil_div(c->W, 4), 128), (unsigned)c->H, (unsigned)n_frames), 128, 0, c->s_copy>>>(a, first_slot);
+    CU_TRY(cudaGetLastError());
+    c->launches += 2;
+    CU_TRY(cudaEventRecord(c->ev_upload, c->s_copy));   // same stream as the uploads: ordered after them, searches wait for this event
+    c->have_upload = true;
+    return ME_OK;
+}
+
+int me_download(me_ctx *c, uint8_t *luma, size_t row_pitch, int first_slot, int n_frames)
+{
+    if (!c || !luma) return fail(ME_EINVAL, "NULL argument");
+    if (n_frames < 1 || first_slot < 0 || first_slot + n_frames > c->max_frames)
+        return fail(ME_EINVAL, "%d frames at slot %d do not fit the %d-slot ring", n_frames, first_slot, c->max_frames);
+    if (row_pitch < (size_t)c->W) return fail(ME_EINVAL, "row_pitch %zu < width %d", row_pitch, c->W);
+    CU_TRY(cudaSetDevice(c->device));
+    CU_TRY(cudaStreamSynchronize(c->s_copy));
+    CU_TRY(cudaMemcpy2D(luma, row_pitch, c->d_frames + (size_t)first_slot * c->frame_stride, c->pitch, (size_t)c->W,
+                        (size_t)n_frames * c->H, cudaMemcpyDeviceToHost));
+    return ME_OK;
 }
 
 int me_search(me_ctx *c, const int32_t *pairs, int n_pairs)

@@ -99,6 +99,16 @@ class MotionEstimator:
         check(self._L.me_upload_bgr(self._ctx, a.ctypes.data, a.strides[1], int(first_slot), a.shape[0]))
         return a.shape[0]
 
+    def clahe(self, first_slot=0, n_frames=1, clip_limit=2.0, tiles=(8, 8)):
+        """CLAHE of ring slots in place on the GPU (cv.createCLAHE(clip_limit, tiles).apply, bit-exact)."""
+        check(self._L.me_clahe(self._ctx, int(first_slot), int(n_frames), float(clip_limit), int(tiles[0]), int(tiles[1])))
+
+    def download(self, first_slot=0, n_frames=1):
+        """Ring slots -> (n_frames,H,W) uint8 host array."""
+        out = np.empty((int(n_frames), self.height, self.width), np.uint8)
+        check(self._L.me_download(self._ctx, out.ctypes.data, out.strides[1], int(first_slot), int(n_frames)))
+        return out
+
     # -- search
     @staticmethod
     def _pairs_arg(pairs):

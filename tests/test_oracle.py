@@ -152,3 +152,28 @@ def test_bgr2gray_matches_cv2():
     rng = np.random.default_rng(3)
     bgr = rng.integers(0, 256, (37, 53, 3), dtype=np.uint8)
     np.testing.assert_array_equal(sad.bgr2gray(bgr), cv2.cvtColor(bgr, cv2.COLOR_BGR2GRAY))
+
+
+@pytest.mark.parametrize("shape,clip,tiles", [((64, 640), 2.0, (8, 8)), ((70, 100), 2.0, (8, 8)), ((64, 100), 2.0, (8, 8)),
+                                             ((33, 47), 2.0, (8, 8)), ((120, 90), 4.0, (4, 6)), ((96, 96), 0.0, (8, 8)),
+                                             ((540, 960), 2.0, (8, 8))])
+def test_clahe_restatement_equals_cv2(shape, clip, tiles):
+    """oracle/clahe_np.py against the library call the reference makes (estimate_vel_vid.py:203-205)."""
+    import cv2
+    from oracle import clahe_np
+    rng = np.random.default_rng(shape[0] * 7 + shape[1])
+    ref = cv2.createCLAHE(clipLimit=clip, tileGridSize=tiles)
+    for img in (rng.integers(0, 256, shape, dtype=np.uint8),
+                cv2.GaussianBlur(rng.integers(0, 256, shape, dtype=np.uint8), (0, 0), 3),
+                (cv2.GaussianBlur(rng.integers(0, 256, shape, dtype=np.uint8), (0, 0), 2) // 12).astype(np.uint8),
+                np.full(shape, 9, np.uint8)):
+        np.testing.assert_array_equal(clahe_np.apply(img, clip, tiles), ref.apply(img))
+
+
+def test_clahe_restatement_on_example_frames(golden_clips):
+    import cv2
+    from oracle import clahe_np
+    ref = cv2.createCLAHE(clipLimit=2.0, tileGridSize=(8, 8))
+    for g in golden_clips.values():
+        for k in (0, 17):
+            np.testing.assert_array_equal(clahe_np.apply(g["frames"][k]), ref.apply(g["frames"][k]))
