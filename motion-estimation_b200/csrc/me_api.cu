@@ -323,6 +323,7 @@ int configure(me_ctx *c)
     if (c->threads % 32 || c->threads < 32 || c->threads > c->kc.maxt)
         return fail(ME_EINVAL, "ME_THREADS=%d is not a multiple of 32 in [32,%d]", c->threads, c->kc.maxt);
     a.use_tma = env_int("ME_NO_TMA", 0) ? 0 : 1;
+    a.repeat = env_int("ME_REPEAT", 1) > 0 ? env_int("ME_REPEAT", 1) : 1;
 
     // Work accounting: nominal = what the ALU executes, valid = in-frame candidates.
     c->cand_px = (long long)a.nb * B * B * U * U;

@@ -83,6 +83,7 @@ struct SearchArgs {
     // gates
     int min_range, min_curv, subpixel, min_valid;
     int use_tma;
+    int repeat;                 // debug (ME_REPEAT): run the candidate phase this many times; results are unchanged
     // outputs
     int16_t *blk_mv;            // [P][nb][2]
     uint32_t *blk_sad;          // [P][nb]
@@ -654,6 +655,7 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     const bool usual = nd == a.full_nd[lasty];
     const unsigned short *grp = a.group[lastx];
     const int n_wide = a.n_wide[lastx], n_narrow = a.n_narrow[lastx];
+    for (int rep = 0; rep < a.repeat; ++rep) {
     if (nd > 0) {   // wide patches: NDY x NQ
         const int per_j = nd * n_wide;
         const int total = nj * per_j;
@@ -686,6 +688,7 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
             run_item<B, NDY, 1, PITCH, 1, K64, RB>(a, active, j, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
                                                    s_key, tile_interior, dyi_lo, dyi_hi, X0, lane, ubase, dbase, slab_w);
         }
+    }
     }
     __syncthreads();
 
