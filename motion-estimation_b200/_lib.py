@@ -47,7 +47,7 @@ class Geometry(C.Structure):
 
 
 def sources():
-    return [os.path.join(_CSRC, "me_api.cu"), os.path.join(_CSRC, "sad_search.cuh"), os.path.join(_CSRC, "clahe.cuh"), HEADER]
+    return [os.path.join(_CSRC, "me_api.cu"), os.path.join(_CSRC, "sad_search.cuh"), os.path.join(_CSRC, "clahe.cuh"), os.path.join(_CSRC, "sad_persistent.cuh"), HEADER]
 
 
 def build(force: bool = False, verbose: bool = False) -> str:

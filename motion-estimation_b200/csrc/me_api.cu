@@ -14,6 +14,7 @@
 
 #include "../../include/me_b200.h"
 #include "sad_search.cuh"
+#include "sad_persistent.cuh"
 #include "clahe.cuh"
 
 namespace {
@@ -77,6 +78,7 @@ int make_tensor_map(CUtensorMap *tm, const uint8_t *base, int W, int H, int n_fr
 
 struct KernelChoice {
     const void *fn = nullptr;
+    const void *fn_persistent = nullptr;   // warp-specialised resident form (32-bit keys only)
     int ndy = 0, nq = 0, maxt = 0, pitch = 0, rank_bits = 0;
 };
 
@@ -88,6 +90,7 @@ KernelChoice choice()
 {
     KernelChoice k;
     k.fn = (const void *)&me::sad_search_kernel<B, kNDY, kNQ, PITCH, K64, RB, kMaxThreads, 3>;
+    if constexpr (!K64 && B <= 16) k.fn_persistent = (const void *)&me::sad_search_persistent<B, kNDY, kNQ, PITCH, K64, RB>;
     k.ndy = kNDY; k.nq = kNQ; k.maxt = kMaxThreads; k.pitch = PITCH; k.rank_bits = RB;
     return k;
 }
@@ -154,6 +157,8 @@ struct me_ctx {
     CUtensorMap tm_win{}, tm_ref{};
     KernelChoice kc{};
     int threads = 0, smem = 0, sm_count = 0, win_pitch = 0;
+    int pstage_bytes = 0, smem_persistent = 0;    // resident kernel: one stage of window copies, total dynamic smem (0 = not usable)
+    int *d_ready = nullptr, *d_error = nullptr;  // resident kernel: queue of completed pairs, wait-timeout flag
     int64_t launches = 0;
     int64_t cand_px = 0, cand_px_valid = 0;
 };
@@ -302,6 +307,11 @@ int configure(me_ctx *c)
                 }
     }
 
+    // resident (persistent) form: two stages of window copies + reduction scratch + control
+    c->pstage_bytes = round_up(a.n_bufs * a.copy_bytes + 128 + 256 + me::kRefPitch * B, 128);
+    c->smem_persistent = me::kStages * c->pstage_bytes + (2 * me::kSelBins + 64) * 4 + 1024;
+    if (c->smem_persistent > 227 * 1024 || !c->kc.fn_persistent || env_int("ME_PERSISTENT", 1) == 0) c->smem_persistent = 0;
+
     {   // fastdiv magics of full slabs (see sad_search.cuh)
         auto magic = [](int d) { return d <= 1 ? 0u : (unsigned)(0x100000000ull / (unsigned)d + 1ull); };
         for (int ly = 0; ly < 2; ++ly) {
@@ -348,10 +358,22 @@ int launch_search(me_ctx *c, const uint8_t *frames, const CUtensorMap &tm_win, c
     me::SearchArgs a = c->args;
     a.frames = frames;
     a.pairs = c->d_pairs;
-    void *params[3] = {(void *)&tm_win, (void *)&tm_ref, (void *)&a};
+    const long long units = (long long)a.tiles_per_pair * n_pairs * a.nsx * a.nsy;
     CU_TRY(cudaEventRecord(c->ev_k0, st));
-    CU_TRY(cudaLaunchKernel(c->kc.fn, dim3((unsigned)(a.tiles_per_pair * n_pairs * a.nsx * a.nsy)), dim3((unsigned)c->threads), params,
-                            (size_t)c->smem, st));
+    if (c->smem_persistent && units >= 2ll * c->sm_count) {
+        // enough work to keep one resident CTA per SM busy: the warp-specialised kernel (sad_persistent.cuh)
+        me::PersistArgs pa;
+        pa.n_units = (int)units; pa.n_pairs = n_pairs; pa.stage_bytes = c->pstage_bytes;
+        pa.ready_pairs = c->d_ready; pa.error_flag = c->d_error;
+        CU_TRY(cudaMemsetAsync(c->d_ready, 0xff, sizeof(int) * (size_t)(n_pairs + 1), st));
+        void *params[4] = {(void *)&tm_win, (void *)&tm_ref, (void *)&a, (void *)&pa};
+        const unsigned grid = units < c->sm_count ? (unsigned)units : (unsigned)c->sm_count;
+        CU_TRY(cudaLaunchKernel(c->kc.fn_persistent, dim3(grid), dim3((unsigned)me::kPersistThreads), params,
+                                (size_t)c->smem_persistent, st));
+    } else {
+        void *params[3] = {(void *)&tm_win, (void *)&tm_ref, (void *)&a};
+        CU_TRY(cudaLaunchKernel(c->kc.fn, dim3((unsigned)units), dim3((unsigned)c->threads), params, (size_t)c->smem, st));
+    }
     CU_TRY(cudaEventRecord(c->ev_k1, st));
     c->launches += 1;
     return ME_OK;
@@ -515,6 +537,13 @@ int me_create(int device, int height, int width, const me_params *params, int ma
         CREATE_TRY(cudaMalloc(&c->args.tile_ticket, nt * sizeof(unsigned)));
         CREATE_TRY(cudaMemset(c->args.tile_ticket, 0, nt * sizeof(unsigned)));
     }
+    CREATE_TRY(cudaMalloc(&c->d_ready, sizeof(int) * (size_t)(max_pairs + 1)));
+    CREATE_TRY(cudaMalloc(&c->d_error, sizeof(int)));
+    CREATE_TRY(cudaMemset(c->d_error, 0, sizeof(int)));
+    if (c->smem_persistent) {
+        CREATE_TRY(cudaFuncSetAttribute(c->kc.fn_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, c->smem_persistent));
+        CREATE_TRY(cudaFuncSetAttribute(c->kc.fn_persistent, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    }
     CREATE_TRY(cudaFuncSetAttribute(c->kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, c->smem));
     CREATE_TRY(cudaFuncSetAttribute(c->kc.fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
 #undef CREATE_TRY
@@ -534,6 +563,7 @@ int me_destroy(me_ctx *c)
     cudaFree(c->d_frames); cudaFree(c->d_bgr); cudaFree(c->d_luts); cudaFree(c->d_pairs);
     cudaFree(c->args.blk_mv); cudaFree(c->args.blk_sad); cudaFree(c->args.blk_sub); cudaFree(c->args.blk_flags);
     cudaFree(c->args.pair_out); cudaFree(c->args.pair_ticket); cudaFree(c->args.blk_key); cudaFree(c->args.tile_ticket);
+    cudaFree(c->d_ready); cudaFree(c->d_error);
     for (int i = 0; i < 2; ++i) {
         if (c->h_stage[i]) cudaFreeHost(c->h_stage[i]);
         if (c->stage_free[i]) cudaEventDestroy(c->stage_free[i]);
@@ -699,7 +729,10 @@ int me_fetch_pairs(me_ctx *c, me_pair_result *out, int n_pairs)
     CU_TRY(cudaSetDevice(c->device));
     CU_TRY(cudaMemcpyAsync(c->h_pair_out, c->args.pair_out, sizeof(me_pair_result) * (size_t)n_pairs,
                            cudaMemcpyDeviceToHost, c->s_compute));
+    int err = 0;
+    CU_TRY(cudaMemcpyAsync(&err, c->d_error, sizeof(int), cudaMemcpyDeviceToHost, c->s_compute));
     CU_TRY(cudaStreamSynchronize(c->s_compute));
+    if (err) return fail(ME_ECUDA, "the resident search kernel gave up waiting for a frame pair to complete (internal error)");
     memcpy(out, c->h_pair_out, sizeof(me_pair_result) * (size_t)n_pairs);
     return ME_OK;
 }
