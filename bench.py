@@ -223,7 +223,7 @@ def run_ours(args):
     alg_bytes = (PAIRS + 1) * H * W + PAIRS * geo["nbx"] * geo["nby"] * 17 + PAIRS * 24
     hbm_gbs = float(peaks["hbm_gbs"])
     roofline = {
-        "bound": "int_alu", "kernel": f"sad_search_kernel<16,5,4,{geo['window_pitch']}>", "achieved": achieved / 1e9, "peak": peak_alu / 1e9,
+        "bound": "int_alu", "kernel": (f"sad_search_persistent<16,5,4,{geo['window_pitch']}>" if geo.get("resident_kernel") else f"sad_search_kernel<16,5,4,{geo['window_pitch']}>"), "achieved": achieved / 1e9, "peak": peak_alu / 1e9,
         "unit": "Gcand*px/s", "frac": achieved / peak_alu, "traffic": traffic,
         "peak_is": f"{sms} SMs x {ipc:.2f} VABSDIFF4 thread-instr/clk/SM (microbenchmarked in this run) x 4 px x "
                    f"{f_max / 1e6:.0f} MHz max SM clock; {peak_src}",

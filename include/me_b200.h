@@ -87,7 +87,8 @@ typedef struct me_geometry {
     int32_t uses_tma;
     int32_t slabs_x, slabs_y;   /* the candidate square is cut into slabs_x * slabs_y CTAs per tile   */
     int32_t window_pitch;       /* bytes per shared-memory window row (a template constant)         */
-    int32_t reserved;
+    int32_t resident_kernel;    /* 1: launches of >= 2*sm_count tiles run the one-CTA-per-SM resident
+                                   kernel (producer warp + consumer warps); 0: always one CTA per tile */
 } me_geometry;
 
 const char *me_last_error(void);          /* thread-local, never NULL                         */

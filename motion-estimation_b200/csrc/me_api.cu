@@ -311,6 +311,14 @@ int configure(me_ctx *c)
     c->pstage_bytes = round_up(a.n_bufs * a.copy_bytes + 128 + 256 + me::kRefPitch * B, 128);
     c->smem_persistent = me::kStages * c->pstage_bytes + (2 * me::kSelBins + 64) * 4 + 1024;
     if (c->smem_persistent > 227 * 1024 || !c->kc.fn_persistent || env_int("ME_PERSISTENT", 1) == 0) c->smem_persistent = 0;
+    if (c->smem_persistent && env_int("ME_PERSISTENT", 1) != 2) {
+        // The resident kernel has ONE producer warp per SM: it only pays when searching a unit takes the
+        // consumer warps clearly longer than loading and shifting its window takes the producer
+        // (r01: +2 % at 1080p/16/+-32, but -40 % at +-8 and -5 % on slabbed searches).
+        const double t_cons = (double)a.tmb * NSUB * U * U * B * B / 256.0;                               // cycles at 64 lanes x 4 px
+        const double t_prod = 6000.0 + (double)a.n_row_boxes * a.box_rows * (c->win_pitch / 16) / 32.0 * 120.0;
+        if (a.nsx * a.nsy > 1 || t_cons < 2.7 * t_prod) c->smem_persistent = 0;
+    }
 
     {   // fastdiv magics of full slabs (see sad_search.cuh)
         auto magic = [](int d) { return d <= 1 ? 0u : (unsigned)(0x100000000ull / (unsigned)d + 1ull); };
@@ -593,7 +601,7 @@ int me_get_geometry(const me_ctx *c, me_geometry *g)
     g->tiles_per_pair = c->args.tiles_per_pair;
     g->cand_px_per_pair = c->cand_px; g->cand_px_per_pair_valid = c->cand_px_valid;
     g->sm_count = c->sm_count; g->uses_tma = c->args.use_tma;
-    g->slabs_x = c->args.nsx; g->slabs_y = c->args.nsy; g->window_pitch = c->win_pitch; g->reserved = 0;
+    g->slabs_x = c->args.nsx; g->slabs_y = c->args.nsy; g->window_pitch = c->win_pitch; g->resident_kernel = c->smem_persistent ? 1 : 0;
     return ME_OK;
 }
 
