@@ -9,8 +9,9 @@ DIR holds the recording (``video.mkv``, else the first ``*.mkv`` / ``*.h264``), 
 ``*tstamps.txt`` and optionally ``*encoder.csv``.  Output is ``velocity_estimates.csv`` with the
 reference's header and row layout (its lines 410, 572, 633-636).  What changed is the engine: the
 per-pair displacement is the CUDA block search instead of cv.findTransformECC, and the recording is
-decoded sequentially into one array.  CLAHE / non-local-means pre-processing (reference lines
-201-299, 99 % of its run time) is outside this path and is not applied unless --clahe is given.
+decoded sequentially into one array.  The reference's CLAHE / non-local-means pre-processing (its lines
+201-299, 99 % of its run time) runs on the GPU, bit-exact with the cv2 calls it replaces, when --clahe /
+--denoise / --preprocess (both) are given; by default the search sees the decoded frames.
 """
 import argparse
 import os
@@ -37,6 +38,8 @@ def parse(argv=None):
     ap.add_argument("--device", type=int, default=0)
     ap.add_argument("--out", type=Path, default=None, help="directory for the CSV (default: DIR, else the cwd)")
     ap.add_argument("--clahe", action="store_true", help="apply CLAHE(2.0,(8,8)) per frame like reference :201-219 (GPU kernels, bit-exact with cv2)")
+    ap.add_argument("--denoise", action="store_true", help="non-local-means denoise like reference :246-299 (h=15, 19/41 windows, 1/5/9 frames; GPU kernel, bit-exact with cv2)")
+    ap.add_argument("--preprocess", action="store_true", help="--clahe and --denoise: the reference's full default pipeline before the pair loop")
     a = ap.parse_args(argv)
     whole = a.useWholeVideo == "True"
     if not whole and len(a.fileIndex) != 2:
@@ -64,9 +67,13 @@ def main(argv=None):
                 sys.exit(f"no *.h264 in {src}")
             target = str(hits[0])
         frames = ingest.read_frames(target, first, last)
-        if a.clahe:                                   # reference lines 201-219, on the GPU, bit-exact with cv2's CLAHE
+        if a.clahe or a.preprocess:                   # reference lines 201-219, on the GPU, bit-exact with cv2's CLAHE
             api.set_defaults(device=a.device)
             frames = api.adaptive_histogram_equalization(frames)
+        if a.denoise or a.preprocess:                 # reference lines 246-299: non-local means, bit-exact with cv2's
+            api.set_defaults(device=a.device)
+            frames = api.denoise_hf5(frames, n_list=len(frames) + 1)      # len(numberList) = frames + 1 (its line 73)
+            np.save(cache, frames) if os.access(src, os.W_OK) else None   # the -c cache (the reference keeps images.h5)
     if len(frames) < 2:
         sys.exit("need at least two frames")
     number_list = list(range(first, first + len(frames) + 1))

@@ -120,6 +120,17 @@ int me_upload_bgr(me_ctx *ctx, const uint8_t *bgr, size_t row_pitch, int first_s
  * uploads issued so far; later searches wait for it. */
 int me_clahe(me_ctx *ctx, int first_slot, int n_frames, double clip_limit, int tiles_x, int tiles_y);
 
+/* Non-local-means denoising of ring slots [first_slot, first_slot + n_frames), in place, on the GPU --
+ * replaces cv.fastNlMeansDenoising(src, h, templateWindowSize, searchWindowSize) and
+ * cv.fastNlMeansDenoisingMulti(srcImgs, k, temporalWindowSize, h, ...) as denoise_hf5 / denoising call them
+ * (estimate_vel_vid.py:226-232, 246-262), bit-exact with OpenCV's 8-bit implementation.
+ * temporal_window[k] (odd; 1 = the single-image function; 0 = leave frame k as it is, it only serves as a
+ * neighbour) is the window of frame k of the call; every frame is denoised from the ORIGINAL neighbours, as
+ * the reference does (it reads eq_arrs, writes a new array).  A window that leaves the call's frames is ME_EINVAL (cv2 raises there).  template_window 7 or
+ * 19 are built; search_window <= 41.  Runs on the copy stream like me_clahe. */
+int me_denoise(me_ctx *ctx, int first_slot, int n_frames, const int32_t *temporal_window, float h,
+               int template_window, int search_window);
+
 /* Copy ring slots back to host memory (row_pitch bytes between rows); waits for pending uploads and CLAHE.
  * The reference keeps every stage's frames as (N,H,W) host arrays (estimate_vel_vid.py:215-219). */
 int me_download(me_ctx *ctx, uint8_t *luma, size_t row_pitch, int first_slot, int n_frames);

@@ -47,7 +47,7 @@ class Geometry(C.Structure):
 
 
 def sources():
-    return [os.path.join(_CSRC, "me_api.cu"), os.path.join(_CSRC, "sad_search.cuh"), os.path.join(_CSRC, "clahe.cuh"), os.path.join(_CSRC, "sad_persistent.cuh"), HEADER]
+    return [os.path.join(_CSRC, "me_api.cu"), os.path.join(_CSRC, "sad_search.cuh"), os.path.join(_CSRC, "clahe.cuh"), os.path.join(_CSRC, "nlm.cuh"), os.path.join(_CSRC, "sad_persistent.cuh"), HEADER]
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
@@ -87,6 +87,7 @@ def lib():
     L.me_upload.argtypes = [vp, vp, C.c_size_t, C.c_int, C.c_int]
     L.me_upload_bgr.argtypes = [vp, vp, C.c_size_t, C.c_int, C.c_int]
     L.me_clahe.argtypes = [vp, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int]
+    L.me_denoise.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_int32), C.c_float, C.c_int, C.c_int]
     L.me_download.argtypes = [vp, vp, C.c_size_t, C.c_int, C.c_int]
     L.me_search.argtypes = [vp, i32p, C.c_int]
     L.me_fetch_pairs.argtypes = [vp, C.POINTER(PairResult), C.c_int]
@@ -104,7 +105,7 @@ def lib():
     L.me_search_static_scratch.argtypes = [vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.POINTER(Params), i32p, C.c_int,
                                            vp, vp]
     L.me_search_static_scratch.restype = C.c_int
-    for name in ("me_clahe", "me_download", "me_create", "me_destroy", "me_get_geometry", "me_upload", "me_upload_bgr", "me_search",
+    for name in ("me_clahe", "me_denoise", "me_download", "me_create", "me_destroy", "me_get_geometry", "me_upload", "me_upload_bgr", "me_search",
                  "me_fetch_pairs", "me_fetch_blocks", "me_estimate_pair", "me_search_device", "me_sync",
                  "me_last_search_ms", "me_microbench_vabsdiff4", "me_timer_start", "me_timer_stop"):
         getattr(L, name).restype = C.c_int

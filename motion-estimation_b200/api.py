@@ -140,6 +140,88 @@ def adaptive_histogram_equalization(noisy_arrs, *, clip_limit: float = 2.0, tile
     return out
 
 
+def reference_windows(n_frames, n_list=None):
+    """Temporal window denoise_hf5 picks for frame k (estimate_vel_vid.py:250-262): the single-image call for the two
+    first and three last frames, 5 frames for k <= 4 or k >= len(numberList) - 5, otherwise 9."""
+    L = n_frames if n_list is None else int(n_list)
+    return [1 if (k <= 1 or k >= L - 3) else 5 if (k <= 4 or k >= L - 5) else 9 for k in range(n_frames)]
+
+
+def _denoise_frames(frames, windows, h, template_window, search_window, device, chunk):
+    """Denoise frames[k] with temporal window windows[k]; device chunks carry the halo frames they need."""
+    n = frames.shape[0]
+    halo = max(w // 2 for w in windows)
+    chunk = max(1, min(chunk, n))
+    eng = _engine(frames.shape[1], frames.shape[2], default_config, default_device if device is None else device,
+                  max(chunk + 2 * halo, 2), 1)
+    out = np.empty_like(frames)
+    for k in range(0, n, chunk):
+        m = min(chunk, n - k)
+        lo, hi = max(0, k - halo), min(n, k + m + halo)
+        eng.upload(frames[lo:hi], first_slot=0)
+        tw = [windows[i] if k <= i < k + m else 0 for i in range(lo, hi)]       # halo frames are only read (window 0)
+        eng.denoise(0, tw, h, template_window, search_window)
+        out[k:k + m] = eng.download(k - lo, m)
+    return out
+
+
+def denoising(arrays, numberIndex, num_frames_window, *, h: float = 15.0, template_window: int = 19, search_window: int = 41,
+              device: Optional[int] = None):
+    """One frame of ``arrays`` denoised from its temporal neighbours -- estimate_vel_vid.py:226-232
+    (cv.fastNlMeansDenoisingMulti(h=15, templateWindowSize=19, searchWindowSize=41)), on the GPU, bit-exact.
+    Raises ValueError where cv2 raises (window leaving the sequence, even window)."""
+    frames = np.ascontiguousarray(arrays, dtype=np.uint8)
+    if frames.ndim != 3:
+        raise ValueError("arrays must be (N, H, W) uint8")
+    half = int(num_frames_window) // 2
+    if num_frames_window % 2 == 0 or numberIndex - half < 0 or numberIndex + half >= len(frames):
+        raise ValueError("temporal window must be odd and lie inside the sequence")
+    sub = frames[numberIndex - half:numberIndex + half + 1]
+    tw = [0] * len(sub)
+    tw[half] = int(num_frames_window)
+    return _denoise_frames(sub, tw, h, template_window, search_window, device, len(sub))[half]
+
+
+def denoise_hf5(eq_arrs, *, n_list: Optional[int] = None, h: float = 15.0, template_window: int = 19, search_window: int = 41,
+                device: Optional[int] = None, chunk: int = 256, h5_path: Optional[str] = None):
+    """(N,H,W) uint8 -> denoised (N,H,W) uint8 -- the role of estimate_vel_vid.py:246-299 on the GPU.
+
+    Frame k gets the reference's choice of call (:250-262, ``n_list`` = len(numberList), default N): the single-image
+    filter at the ends, the 5-frame and then the 9-frame temporal window inside.  Where the reference's call would
+    raise (window leaving the array because the video was shorter than numberList) it prints and stops (:263-266);
+    the same truncation happens here.  ``h5_path`` writes the ``clean_images`` dataset like :287-297 when h5py is
+    importable (it is not in this image)."""
+    frames = np.ascontiguousarray(eq_arrs, dtype=np.uint8)
+    if frames.ndim != 3:
+        raise ValueError("eq_arrs must be (N, H, W) uint8")
+    n = frames.shape[0]
+    windows = reference_windows(n, n_list)
+    for k, w in enumerate(windows):                       # first frame whose call would throw ends the sequence
+        if k - w // 2 < 0 or k + w // 2 >= n:
+            print("something went wrong with denoising")
+            n = k
+            break
+    if n == 0:
+        return frames[:0].copy()
+    out = _denoise_frames(frames, windows[:n] + [0] * (frames.shape[0] - n), h, template_window, search_window, device, chunk)[:n]
+    if h5_path is not None:
+        try:
+            import h5py
+        except ImportError:
+            print(f"h5py is not installed: {h5_path} not written")
+        else:
+            with h5py.File(h5_path, "w") as f:
+                ds = f.create_dataset("clean_images", data=out, maxshape=(len(out) + 10,) + out.shape[1:],
+                                      chunks=(min(10, len(out)),) + out.shape[1:], dtype="uint8", compression="gzip",
+                                      compression_opts=7, shuffle=True)
+                ds.attrs["CLASS"] = "IMAGE"
+                ds.attrs["IMAGE_VERSION"] = "1.2"
+                ds.attrs["IMAGE_SUBCLASS"] = "IMAGE_GRAYSCALE"
+                ds.attrs["IMAGE_MINMAXRANGE"] = np.array([0, 255], dtype=np.uint8)
+                ds.attrs["IMAGE_WHITE_IS_ZERO"] = 0
+    return out
+
+
 class _RingSource:
     """d(anchor, k) for a host frame stack through a bounded device ring.
 

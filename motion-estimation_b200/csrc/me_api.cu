@@ -9,13 +9,17 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <algorithm>
+#include <cmath>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/me_b200.h"
 #include "sad_search.cuh"
 #include "sad_persistent.cuh"
 #include "clahe.cuh"
+#include "nlm.cuh"
 
 namespace {
 
@@ -139,6 +143,8 @@ struct me_ctx {
     size_t d_bgr_bytes = 0;
     uint8_t *d_luts = nullptr;          // CLAHE lookup tables, allocated on first use
     size_t d_luts_bytes = 0;
+    uint8_t *d_nlm = nullptr;           // denoised frames + accumulators + tables of me_denoise, allocated on first use
+    size_t d_nlm_bytes = 0;
     // streams / events
     cudaStream_t s_copy = nullptr, s_compute = nullptr;
     cudaEvent_t ev_upload = nullptr, ev_search = nullptr, ev_k0 = nullptr, ev_k1 = nullptr;
@@ -462,6 +468,44 @@ int upload_impl(me_ctx *c, const uint8_t *src, size_t row_pitch, int first_slot,
 
 } // namespace
 
+namespace {
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// OpenCV's almost_dist2weight table for one temporal window size (oracle/nlm_np.py: weight_table)
+void nlm_weight_table(float h, int tws, int sws, int n_frames, std::vector<int> &table, int &shift)
+{
+    const long long max_est = (long long)n_frames * sws * sws * 255;
+    const int fixed = (int)std::min<long long>(INT32_MAX / max_est, INT32_MAX);
+    const int area = tws * tws;
+    shift = 0;
+    while ((1 << shift) < area) ++shift;
+    const double mult = (double)(1 << shift) / area;
+    const int n = (int)(65025 / mult + 1);
+    const float hh = h * h;
+    table.clear();
+    int last = 0;
+    for (int a = 0; a < n; ++a) {
+        double w = std::exp(-(a * mult) / (double)hh);
+        if (std::isnan(w)) w = 1.0;
+        int wt = (int)std::nearbyint(fixed * w);                   // cvRound: round half to even
+        if (wt < 0.001 * fixed) wt = 0;
+        table.push_back(wt);
+        if (wt) last = a;
+    }
+    table.resize((size_t)last + 1);
+}
+
+template <int TWS> int nlm_launch(const me::NlmArgs &a, dim3 grid, size_t smem, cudaStream_t s)
+{
+    CU_TRY(cudaFuncSetAttribute(me::nlm_kernel<TWS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    me::nlm_kernel<TWS><<<grid, me::kNlmThreads, smem, s>>>(a);
+    CU_TRY(cudaGetLastError());
+    return ME_OK;
+}
+
+}  // namespace
+
 extern "C" {
 
 const char *me_last_error(void) { return g_err; }
@@ -568,7 +612,7 @@ int me_destroy(me_ctx *c)
     cudaSetDevice(c->device);
     if (c->s_copy) cudaStreamSynchronize(c->s_copy);
     if (c->s_compute) cudaStreamSynchronize(c->s_compute);
-    cudaFree(c->d_frames); cudaFree(c->d_bgr); cudaFree(c->d_luts); cudaFree(c->d_pairs);
+    cudaFree(c->d_frames); cudaFree(c->d_bgr); cudaFree(c->d_luts); cudaFree(c->d_nlm); cudaFree(c->d_pairs);
     cudaFree(c->args.blk_mv); cudaFree(c->args.blk_sad); cudaFree(c->args.blk_sub); cudaFree(c->args.blk_flags);
     cudaFree(c->args.pair_out); cudaFree(c->args.pair_ticket); cudaFree(c->args.blk_key); cudaFree(c->args.tile_ticket);
     cudaFree(c->d_ready); cudaFree(c->d_error);
@@ -654,6 +698,103 @@ int me_clahe(me_ctx *c, int first_slot, int n_frames, double clip_limit, int til
     CU_TRY(cudaGetLastError());
     c->launches += 2;
     CU_TRY(cudaEventRecord(c->ev_upload, c->s_copy));   // same stream as the uploads: ordered after them, searches wait for this event
+    c->have_upload = true;
+    return ME_OK;
+}
+
+int me_denoise(me_ctx *c, int first_slot, int n_frames, const int32_t *temporal_window, float h, int template_window, int search_window)
+{
+    if (!c || !temporal_window) return fail(ME_EINVAL, "NULL argument");
+    if (n_frames < 1 || first_slot < 0 || first_slot + n_frames > c->max_frames)
+        return fail(ME_EINVAL, "%d frames at slot %d do not fit the %d-slot ring", n_frames, first_slot, c->max_frames);
+    const int tws = 2 * (template_window / 2) + 1, sws = 2 * (search_window / 2) + 1, th = tws / 2, sh = sws / 2;
+    if (template_window < 1 || search_window < 1 || !(h >= 0)) return fail(ME_EINVAL, "template %d / search %d / h %g", template_window, search_window, (double)h);
+    if (tws != 7 && tws != 19) return fail(ME_EUNSUPPORTED, "template window %d: 7 and 19 are built", template_window);
+    if (sws > 41) return fail(ME_EUNSUPPORTED, "search window %d: up to 41 is built", search_window);
+    for (int k = 0; k < n_frames; ++k) {
+        const int t = temporal_window[k];
+        if (t == 0) continue;
+        if (t > 1 && (template_window % 2 == 0 || search_window % 2 == 0))
+            return fail(ME_EINVAL, "frame %d: temporal windows need odd template / search windows (%d / %d), as in OpenCV", k, template_window, search_window);
+        if (t < 1 || t % 2 == 0 || k - t / 2 < 0 || k + t / 2 >= n_frames)
+            return fail(ME_EINVAL, "frame %d: temporal window %d must be 0 or odd and stay inside the %d frames of the call", k, t, n_frames);
+    }
+    CU_TRY(cudaSetDevice(c->device));
+
+    // weight tables, one per distinct temporal window
+    std::vector<int> luts, off(n_frames), len(n_frames);
+    std::vector<std::pair<int, std::pair<int, int>>> seen;
+    int shift = 0;
+    for (int k = 0; k < n_frames; ++k) {
+        const int t = temporal_window[k];
+        if (t == 0) { off[k] = len[k] = 0; continue; }
+        bool found = false;
+        for (auto &e : seen) if (e.first == t) { off[k] = e.second.first; len[k] = e.second.second; found = true; }
+        if (found) continue;
+        std::vector<int> tab;
+        nlm_weight_table(h, tws, sws, t, tab, shift);
+        off[k] = (int)luts.size(); len[k] = (int)tab.size();
+        seen.push_back({t, {off[k], len[k]}});
+        luts.insert(luts.end(), tab.begin(), tab.end());
+    }
+
+    me::NlmArgs a{};
+    a.src = c->d_frames; a.frame_stride = (long long)c->frame_stride; a.pitch = (int)c->pitch; a.W = c->W; a.H = c->H;
+    a.first_slot = first_slot; a.sh = sh; a.shift = shift;
+    const int b = sh + th;
+    a.itp = (me::kNlmTW + 2 * b + 3) / 4 * 4;
+    if ((a.itp / 4) % 2 == 0) a.itp += 4;                       // odd word pitch: lanes on consecutive rows hit distinct banks
+    a.it_rows = me::kNlmTR + 2 * b;
+    const int nr = me::kNlmTR + 2 * th;
+    const size_t smem = (size_t)nr * (me::kNlmTW + 4) * 4 + (size_t)a.it_rows * a.itp + 16;
+    const int tiles = ceil_div(c->W, me::kNlmTW) * ceil_div(c->H, me::kNlmTR);
+    a.nsplit = 1;
+    if ((long long)tiles * n_frames < 2ll * c->sm_count) a.nsplit = std::min(sws, (int)ceil_div(2 * c->sm_count, tiles * n_frames));
+    a.nsplit = env_int("ME_NLM_SPLIT", a.nsplit);
+    if (a.nsplit < 1) a.nsplit = 1;
+
+    // device scratch: [dst frames | acc | twin | lut_off | lut_len | luts]
+    const size_t dst_bytes = (size_t)n_frames * c->H * c->pitch;
+    const size_t acc_bytes = a.nsplit > 1 ? (size_t)n_frames * c->H * c->W * 8 : 0;
+    const size_t meta_bytes = (3 * (size_t)n_frames + luts.size()) * 4;
+    const size_t need = align_up(dst_bytes, 256) + align_up(acc_bytes, 256) + meta_bytes;
+    if (c->d_nlm_bytes < need) {
+        CU_TRY(cudaStreamSynchronize(c->s_copy));
+        if (c->d_nlm) CU_TRY(cudaFree(c->d_nlm));
+        c->d_nlm = nullptr; c->d_nlm_bytes = 0;
+        CU_TRY(cudaMalloc(&c->d_nlm, need));
+        c->d_nlm_bytes = need;
+    }
+    a.dst = c->d_nlm;
+    a.acc = reinterpret_cast<int *>(c->d_nlm + align_up(dst_bytes, 256));
+    int *d_meta = reinterpret_cast<int *>(c->d_nlm + align_up(dst_bytes, 256) + align_up(acc_bytes, 256));
+    std::vector<int> meta;
+    meta.insert(meta.end(), temporal_window, temporal_window + n_frames);
+    meta.insert(meta.end(), off.begin(), off.end());
+    meta.insert(meta.end(), len.begin(), len.end());
+    meta.insert(meta.end(), luts.begin(), luts.end());
+    a.twin = d_meta; a.lut_off = d_meta + n_frames; a.lut_len = d_meta + 2 * n_frames; a.luts = d_meta + 3 * n_frames;
+
+    for (auto &r : c->recent)                        // the frames are rewritten in place: wait for searches that read them
+        if (r.used && r.lo < first_slot + n_frames && r.hi >= first_slot) CU_TRY(cudaStreamWaitEvent(c->s_copy, r.done, 0));
+    CU_TRY(cudaStreamSynchronize(c->s_copy));        // meta is pageable host memory: keep the copy below synchronous with it
+    CU_TRY(cudaMemcpyAsync(d_meta, meta.data(), meta_bytes, cudaMemcpyHostToDevice, c->s_copy));
+    CU_TRY(cudaStreamSynchronize(c->s_copy));
+    if (a.nsplit > 1) CU_TRY(cudaMemsetAsync(a.acc, 0, acc_bytes, c->s_copy));
+    const dim3 grid((unsigned)ceil_div(c->W, me::kNlmTW), (unsigned)ceil_div(c->H, me::kNlmTR), (unsigned)(n_frames * a.nsplit));
+    int rc = tws == 19 ? nlm_launch<19>(a, grid, smem, c->s_copy) : nlm_launch<7>(a, grid, smem, c->s_copy);
+    if (rc) return rc;
+    c->launches += 1;
+    if (a.nsplit > 1) {
+        me::NlmArgs f = a;
+        const long long n_px = (long long)n_frames * c->H * c->W;
+        me::nlm_finish_kernel<<<(unsigned)((n_px + 255) / 256), 256, 0, c->s_copy>>>(f, n_px);
+        CU_TRY(cudaGetLastError());
+        c->launches += 1;
+    }
+    CU_TRY(cudaMemcpy2DAsync(c->d_frames + (size_t)first_slot * c->frame_stride, c->pitch, c->d_nlm, c->pitch, (size_t)c->W,
+                             (size_t)n_frames * c->H, cudaMemcpyDeviceToDevice, c->s_copy));
+    CU_TRY(cudaEventRecord(c->ev_upload, c->s_copy));
     c->have_upload = true;
     return ME_OK;
 }

@@ -1,0 +1,209 @@
+// nlm.cuh -- non-local-means denoising of ring frames (single image and temporal window).
+//
+// Replaces cv.fastNlMeansDenoising / cv.fastNlMeansDenoisingMulti(h=15, templateWindowSize=19,
+// searchWindowSize=41, temporalWindowSize=5|9) as denoise_hf5 / denoising call them
+// (estimate_vel_vid.py:226-232, 246-262) -- 99 % of the reference's wall time (1.9 s per 640x64 frame).
+// Bit-exact with OpenCV's 8-bit implementation (restated in oracle/nlm_np.py and pinned against cv2 there):
+// squared-difference patch distance summed exactly over the template window, weight table indexed by
+// dist >> shift, 32-bit fixed-point accumulation, one rounded division.
+//
+// nlm_kernel<TWS>: one CTA of 256 threads owns a 64x128 tile of output pixels and walks the whole search
+// volume (frame, dy, dx).  The displaced frame's region (tile + template + search halo, reflect-101 at the
+// frame edge) sits in shared memory; per offset
+//   pass A  (row, 16-column segment) tasks: |a-b| of 4 pixels per VABSDIFF4, squares with IMAD, a sliding
+//           TWS-wide horizontal sum, 16 sums stored as 4 x STS.128; the words of the frame being denoised
+//           stay in registers for the whole kernel (they do not depend on the offset);
+//   pass B  one thread per (column, 32-row half): sliding TWS-high vertical sum of pass A's rows, weight
+//           lookup, est += w * pixel, wsum += w with the 64 accumulators in registers.
+// Integer-ALU/shared-memory bound: about 20 thread-instructions per output pixel per offset; HBM traffic
+// is the tile regions once per temporal frame (nothing per offset).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace me {
+
+struct NlmArgs {
+    const uint8_t *src;         // ring base
+    long long frame_stride;
+    int pitch, W, H;
+    int first_slot;             // ring slot of frame 0 of this call
+    uint8_t *dst;               // [n][H][pitch] denoised frames (scratch, copied back by the host)
+    const int *twin;            // [n] temporal window (odd) of each frame; 0 = copy the frame through
+    const int *lut_off;         // [n] offset of the frame's weight table in luts
+    const int *lut_len;         // [n] entries before the table turns to zero
+    const int *luts;
+    int sh;                     // search window half size
+    int shift;                  // dist >> shift indexes the table
+    int itp, it_rows;           // shared region: row pitch in bytes (odd number of words), rows
+    int nsplit;                 // CTAs per tile along the (frame, dy) axis; > 1 accumulates through acc
+    int *acc;                   // [n][H][W][2] (est, wsum), zeroed by the host when nsplit > 1
+};
+
+__device__ __forceinline__ int reflect101_iter(int p, int n)
+{
+    if (n == 1) return 0;
+    while ((unsigned)p >= (unsigned)n) p = p < 0 ? -p : 2 * n - 2 - p;     // OpenCV iterates for borders wider than the frame
+    return p;
+}
+
+constexpr int kNlmK = 32, kNlmRS = 2, kNlmTW = 128, kNlmTR = kNlmK * kNlmRS, kNlmS = 16, kNlmThreads = 256;
+
+template <int TWS>
+__global__ void __launch_bounds__(kNlmThreads, 2) nlm_kernel(const NlmArgs a)
+{
+    constexpr int TH = TWS / 2, K = kNlmK, TW = kNlmTW, TR = kNlmTR, NR = TR + 2 * TH, S = kNlmS, NSEG = TW / S,
+                  NTASK = NSEG * NR, ROUNDS = (NTASK + kNlmThreads - 1) / kNlmThreads, NPX = S + TWS - 1, NW = (NPX + 3) / 4,
+                  HP = TW + 4;                                   // HP = 4 mod 32: conflict-free STS.128 from lanes on consecutive rows
+    extern __shared__ __align__(16) unsigned char nlm_smem[];
+    int *s_h = reinterpret_cast<int *>(nlm_smem);                // NR x HP horizontal sums
+    unsigned char *s_it = nlm_smem + NR * HP * 4;               // it_rows x itp displaced-frame region
+
+    const int tid = threadIdx.x;
+    const int n = blockIdx.z / a.nsplit, sp = blockIdx.z - n * a.nsplit;
+    const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TR;
+    const int sh = a.sh, sws = 2 * sh + 1, b = sh + TH;
+    const int T = a.twin[n], half = T / 2;
+    const int *lut = a.luts + a.lut_off[n];
+    const int lut_n = a.lut_len[n];
+    const uint8_t *main_f = a.src + (long long)(a.first_slot + n) * a.frame_stride;
+    const int itw = a.itp >> 2;
+
+    if (T == 0) {                                                 // window 0: the frame is only a neighbour, pass it through
+        if (sp == 0)
+            for (int idx = tid; idx < TR * TW; idx += kNlmThreads) {
+                const int gy = y0 + idx / TW, gx = x0 + idx % TW;
+                if (gy < a.H && gx < a.W) a.dst[((long long)n * a.H + gy) * a.pitch + gx] = main_f[(size_t)gy * a.pitch + gx];
+            }
+        return;
+    }
+
+    // words of the frame being denoised that this thread's pass-A tasks compare against (offset independent)
+    uint32_t i0[ROUNDS][NW];
+#pragma unroll
+    for (int rd = 0; rd < ROUNDS; ++rd) {
+        const int task = tid + rd * kNlmThreads;
+        const int seg = task / NR, r = task - seg * NR;
+        const uint8_t *row = main_f + (size_t)reflect101_iter(y0 - TH + r, a.H) * a.pitch;
+#pragma unroll
+        for (int k = 0; k < NW; ++k) {
+            uint32_t w = 0;
+            if (task < NTASK)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) w |= (uint32_t)row[reflect101_iter(x0 - TH + seg * S + 4 * k + q, a.W)] << (8 * q);
+            i0[rd][k] = w;
+        }
+    }
+
+    int est[K], wsum[K];
+#pragma unroll
+    for (int i = 0; i < K; ++i) est[i] = wsum[i] = 0;
+
+    const int rows_all = T * sws;
+    const int per = (rows_all + a.nsplit - 1) / a.nsplit;
+    const int row_lo = sp * per, row_hi = min(rows_all, row_lo + per);
+    const int j = tid & (TW - 1), rh = tid / TW;
+    int cur_t = -1;
+
+    for (int orow = row_lo; orow < row_hi; ++orow) {
+        const int ti = orow / sws, dy = orow - ti * sws - sh;
+        if (ti != cur_t) {                                        // stage the next temporal frame's region
+            cur_t = ti;
+            const uint8_t *f = main_f + (long long)(ti - half) * a.frame_stride;
+            __syncthreads();
+            for (int idx = tid; idx < a.it_rows * itw; idx += kNlmThreads) {
+                const int rr = idx / itw, wc = idx - rr * itw;
+                const uint8_t *row = f + (size_t)reflect101_iter(y0 - b + rr, a.H) * a.pitch;
+                uint32_t w = 0;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) w |= (uint32_t)row[reflect101_iter(x0 - b + 4 * wc + q, a.W)] << (8 * q);
+                reinterpret_cast<uint32_t *>(s_it)[idx] = w;
+            }
+            __syncthreads();
+        }
+        for (int dx = -sh; dx <= sh; ++dx) {
+            // ---- pass A: horizontal TWS-sums of squared differences
+#pragma unroll
+            for (int rd = 0; rd < ROUNDS; ++rd) {
+                const int task = tid + rd * kNlmThreads;
+                if (task < NTASK) {
+                    const int seg = task / NR, r = task - seg * NR;
+                    const int start = seg * S + dx + sh;
+                    const uint32_t *row = reinterpret_cast<const uint32_t *>(s_it + (r + sh + dy) * a.itp) + (start >> 2);
+                    const int sft = (start & 3) * 8;
+                    uint32_t w[NW + 1], d[NW];
+#pragma unroll
+                    for (int k = 0; k <= NW; ++k) w[k] = row[k];
+#pragma unroll
+                    for (int k = 0; k < NW; ++k) d[k] = __vabsdiffu4(i0[rd][k], __funnelshift_r(w[k], w[k + 1], sft));
+                    int px[NPX];
+#pragma unroll
+                    for (int x = 0; x < NPX; ++x) px[x] = (int)((d[x >> 2] >> (8 * (x & 3))) & 255u);
+                    int sum = 0;
+#pragma unroll
+                    for (int x = 0; x < TWS; ++x) sum += px[x] * px[x];
+                    int out[S];
+                    out[0] = sum;
+#pragma unroll
+                    for (int c = 1; c < S; ++c) {
+                        sum += px[c + TWS - 1] * px[c + TWS - 1];
+                        sum -= px[c - 1] * px[c - 1];
+                        out[c] = sum;
+                    }
+                    int4 *dstp = reinterpret_cast<int4 *>(s_h + r * HP + seg * S);
+#pragma unroll
+                    for (int e = 0; e < S / 4; ++e) dstp[e] = make_int4(out[4 * e], out[4 * e + 1], out[4 * e + 2], out[4 * e + 3]);
+                }
+            }
+            __syncthreads();
+            // ---- pass B: vertical TWS-sums, weights, accumulation
+            {
+                const int *hp = s_h + (rh * K) * HP + j;
+                const unsigned char *pp = s_it + (rh * K + b + dy) * a.itp + (j + b + dx);
+                int v = 0;
+#pragma unroll
+                for (int r = 0; r < TWS; ++r) v += hp[r * HP];
+#pragma unroll
+                for (int i = 0; i < K; ++i) {
+                    const int ad = v >> a.shift;
+                    if (ad < lut_n) {
+                        const int wgt = __ldg(lut + ad);
+                        est[i] += wgt * (int)pp[i * a.itp];
+                        wsum[i] += wgt;
+                    }
+                    if (i + 1 < K) v += hp[(i + TWS) * HP] - hp[i * HP];
+                }
+            }
+            __syncthreads();
+        }
+    }
+
+    const int gx = x0 + j;
+    if (gx >= a.W) return;
+#pragma unroll
+    for (int i = 0; i < K; ++i) {
+        const int gy = y0 + rh * K + i;
+        if (gy >= a.H) break;
+        if (a.nsplit > 1) {
+            int *acc = a.acc + (((long long)n * a.H + gy) * a.W + gx) * 2;
+            if (wsum[i]) { atomicAdd(acc, est[i]); atomicAdd(acc + 1, wsum[i]); }
+        } else {
+            const unsigned q = ((unsigned)est[i] + (unsigned)wsum[i] / 2u) / (unsigned)wsum[i];
+            a.dst[((long long)n * a.H + gy) * a.pitch + gx] = (uint8_t)min(q, 255u);
+        }
+    }
+}
+
+// nsplit > 1: turn the accumulated (est, wsum) into pixels
+__global__ void __launch_bounds__(256) nlm_finish_kernel(const NlmArgs a, long long n_px)
+{
+    const long long p = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (p >= n_px) return;
+    const long long row = p / a.W;
+    const int x = (int)(p - row * a.W);
+    if (a.twin[row / a.H] == 0) return;                          // passed through by nlm_kernel
+    const unsigned est = (unsigned)a.acc[2 * p], ws = (unsigned)a.acc[2 * p + 1];
+    a.dst[row * a.pitch + x] = (uint8_t)min((est + ws / 2u) / ws, 255u);
+}
+
+}  // namespace me

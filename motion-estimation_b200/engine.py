@@ -103,6 +103,13 @@ class MotionEstimator:
         """CLAHE of ring slots in place on the GPU (cv.createCLAHE(clip_limit, tiles).apply, bit-exact)."""
         check(self._L.me_clahe(self._ctx, int(first_slot), int(n_frames), float(clip_limit), int(tiles[0]), int(tiles[1])))
 
+    def denoise(self, first_slot, temporal_windows, h=15.0, template_window=19, search_window=41):
+        """Non-local-means denoising of len(temporal_windows) ring slots in place on the GPU
+        (cv.fastNlMeansDenoising / ...Multi with temporalWindowSize = temporal_windows[k], bit-exact)."""
+        tw = np.ascontiguousarray(temporal_windows, np.int32)
+        check(self._L.me_denoise(self._ctx, int(first_slot), int(tw.size), tw.ctypes.data_as(C.POINTER(C.c_int32)),
+                                 float(h), int(template_window), int(search_window)))
+
     def download(self, first_slot=0, n_frames=1):
         """Ring slots -> (n_frames,H,W) uint8 host array."""
         out = np.empty((int(n_frames), self.height, self.width), np.uint8)

@@ -51,6 +51,27 @@ def test_estimate_vel_vid_cli(recording, tmp_path):
     np.testing.assert_allclose([r[0] for r in ref_units.out_information][1:], want / 2, rtol=0.01)   # half-resolution unit
 
 
+def test_estimate_vel_vid_cli_preprocess(recording, tmp_path):
+    """--preprocess = the reference's default pipeline: CLAHE, non-local means, then the pair loop; the cache it
+    leaves (images.npy, the role of images.h5) holds what cv2 produces from the same frames, and -c reuses it."""
+    import cv2
+    d, frames = recording
+    out = tmp_path / "out3"
+    res = _load("estimate_vel_vid").main(["0", "14", "-p", d, "--out", str(out), "--units", "fullres", "--range", "16", "--preprocess"])
+    clean = np.load(os.path.join(d, "images.npy"))
+    assert clean.shape == (14, 64, 320)
+    clahe = cv2.createCLAHE(clipLimit=2.0, tileGridSize=(8, 8))
+    eq = np.stack([clahe.apply(z) for z in frames[:14]])
+    for k, T in ((0, 1), (3, 5), (6, 9), (10, 5), (13, 1)):
+        want = cv2.fastNlMeansDenoising(src=eq[k], h=15, templateWindowSize=19, searchWindowSize=41) if T == 1 else \
+            cv2.fastNlMeansDenoisingMulti(srcImgs=eq, imgToDenoiseIndex=k, temporalWindowSize=T, h=15, templateWindowSize=19, searchWindowSize=41)
+        np.testing.assert_array_equal(clean[k], want, err_msg=f"frame {k}")
+    want_v = (7.0 / 611) / (5.531e-3 / 60)
+    np.testing.assert_allclose([r[0] for r in res.out_information][1:], want_v, rtol=0.02)
+    again = _load("estimate_vel_vid").main(["0", "14", "-p", d, "--out", str(out), "--units", "fullres", "--range", "16", "-c"])
+    assert [tuple(r) for r in again.out_information] == [tuple(r) for r in res.out_information]
+
+
 def test_estimate_vel_cli(recording, tmp_path):
     d, frames = recording
     out = tmp_path / "out2"

@@ -177,3 +177,31 @@ def test_clahe_restatement_on_example_frames(golden_clips):
     for g in golden_clips.values():
         for k in (0, 17):
             np.testing.assert_array_equal(clahe_np.apply(g["frames"][k]), ref.apply(g["frames"][k]))
+
+
+@pytest.mark.parametrize("shape,T,k,h,tw,sw", [((20, 33), 1, 0, 15, 19, 41), ((20, 33), 5, 2, 15, 19, 41), ((20, 33), 9, 4, 15, 19, 41),
+                                               ((37, 50), 3, 1, 10, 7, 21), ((37, 50), 1, 2, 3, 7, 21), ((30, 30), 3, 2, 30, 5, 11)])
+def test_nlm_restatement_equals_cv2(shape, T, k, h, tw, sw):
+    """oracle/nlm_np.py against the library calls the reference makes (estimate_vel_vid.py:226-232, 251-262)."""
+    import cv2
+    from oracle import nlm_np
+    rng = np.random.default_rng(sum(shape) + T)
+    base = cv2.GaussianBlur(rng.integers(0, 256, shape).astype(np.uint8), (0, 0), 2).astype(np.float64) * 1.5 - 60
+    frames = np.clip(base[None] + rng.normal(0, 10, (max(2 * k + 1, T + k),) + shape), 0, 255).astype(np.uint8)
+    if T == 1:
+        ref = cv2.fastNlMeansDenoising(src=frames[k], h=h, templateWindowSize=tw, searchWindowSize=sw)
+    else:
+        ref = cv2.fastNlMeansDenoisingMulti(srcImgs=frames, imgToDenoiseIndex=k, temporalWindowSize=T, h=h,
+                                            templateWindowSize=tw, searchWindowSize=sw)
+    got = nlm_np.denoise(frames, k, T, h, tw, sw)
+    assert h < 5 or (ref != frames[k]).mean() > 0.5               # the filter did something (h=3 is below the noise: identity)
+    np.testing.assert_array_equal(got, ref)
+
+
+def test_nlm_reference_window_rule():
+    """Which call denoise_hf5 makes for frame k (estimate_vel_vid.py:250-262)."""
+    from oracle import nlm_np
+    assert nlm_np.reference_windows(12) == [1, 1, 5, 5, 5, 9, 9, 5, 5, 1, 1, 1]
+    assert nlm_np.reference_windows(11, 12) == [1, 1, 5, 5, 5, 9, 9, 5, 5, 1, 1]     # len(numberList) = frames + 1 in the scripts
+    with pytest.raises(ValueError):
+        nlm_np.denoise(np.zeros((3, 8, 8), np.uint8), 0, 3)
