@@ -138,7 +138,7 @@ __global__ void __launch_bounds__(kNlmThreads, 2) nlm_kernel(const NlmArgs a)
                     for (int k = 0; k < NW; ++k) d[k] = __vabsdiffu4(i0[rd][k], __funnelshift_r(w[k], w[k + 1], sft));
                     int px[NPX];
 #pragma unroll
-                    for (int x = 0; x < NPX; ++x) px[x] = (int)((d[x >> 2] >> (8 * (x & 3))) & 255u);
+                    for (int x = 0; x < NPX; ++x) px[x] = (int)__byte_perm(d[x >> 2], 0u, 0x4440u | (unsigned)(x & 3));   // one PRMT per pixel
                     int sum = 0;
 #pragma unroll
                     for (int x = 0; x < TWS; ++x) sum += px[x] * px[x];
@@ -166,11 +166,10 @@ __global__ void __launch_bounds__(kNlmThreads, 2) nlm_kernel(const NlmArgs a)
 #pragma unroll
                 for (int i = 0; i < K; ++i) {
                     const int ad = v >> a.shift;
-                    if (ad < lut_n) {
-                        const int wgt = __ldg(lut + ad);
-                        est[i] += wgt * (int)pp[i * a.itp];
-                        wsum[i] += wgt;
-                    }
+                    int wgt = 0;
+                    if (ad < lut_n) wgt = __ldg(lut + ad);            // one predicated load, no divergent region
+                    est[i] += wgt * (int)pp[i * a.itp];
+                    wsum[i] += wgt;
                     if (i + 1 < K) v += hp[(i + TWS) * HP] - hp[i * HP];
                 }
             }

@@ -1,4 +1,5 @@
-"""Time me_denoise on a batch of frames: python tools/time_nlm.py H W N [T]   (T = temporal window for inner frames)"""
+"""Time me_denoise on a batch of frames: python tools/time_nlm.py H W N [T] [smooth]   (T = temporal window for inner frames;
+"smooth" = low-noise frames where most patches are similar and every weight lookup is taken)"""
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
@@ -7,6 +8,8 @@ H, W, N = map(int, sys.argv[1:4])
 T = int(sys.argv[4]) if len(sys.argv) > 4 else 9
 rng = np.random.default_rng(0)
 frames = rng.integers(0, 256, (N, H, W), dtype=np.uint8)
+if len(sys.argv) > 5:
+    frames = (128 + rng.normal(0, 4, (N, H, W))).astype(np.uint8)
 half = T // 2
 windows = [T if half <= k < N - half else 1 for k in range(N)]
 with me.MotionEstimator(max(H, 16), max(W, 16), me.SearchConfig(16, 4), max_frames=N, max_pairs=1) as est:
