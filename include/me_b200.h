@@ -80,7 +80,7 @@ typedef struct me_geometry {
     int32_t tile_blocks_x;      /* blocks per CTA tile                                        */
     int32_t threads_per_cta;
     int32_t smem_bytes;
-    int32_t tiles_per_pair;     /* == CTAs per pair                                           */
+    int32_t tiles_per_pair;     /* tiles per pair; CTAs per pair = tiles * slabs_x * slabs_y  */
     int64_t cand_px_per_pair;         /* blocks * B^2 * (2R+1)^2 (nominal, what the ALU executes) */
     int64_t cand_px_per_pair_valid;   /* in-frame candidates only (algorithmic work)              */
     int32_t sm_count;
@@ -89,6 +89,7 @@ typedef struct me_geometry {
     int32_t window_pitch;       /* bytes per shared-memory window row (a template constant)         */
     int32_t resident_kernel;    /* 1: launches of >= 2*sm_count tiles run the one-CTA-per-SM resident
                                    kernel (producer warp + consumer warps); 0: always one CTA per tile */
+    int32_t tile_blocks_y;      /* block rows per CTA tile (> 1 for small ranges: the rows share the halo) */
 } me_geometry;
 
 const char *me_last_error(void);          /* thread-local, never NULL                         */

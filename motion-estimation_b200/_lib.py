@@ -43,7 +43,7 @@ class Geometry(C.Structure):
                 ("threads_per_cta", C.c_int32), ("smem_bytes", C.c_int32), ("tiles_per_pair", C.c_int32),
                 ("cand_px_per_pair", C.c_int64), ("cand_px_per_pair_valid", C.c_int64),
                 ("sm_count", C.c_int32), ("uses_tma", C.c_int32), ("slabs_x", C.c_int32), ("slabs_y", C.c_int32),
-                ("window_pitch", C.c_int32), ("resident_kernel", C.c_int32)]
+                ("window_pitch", C.c_int32), ("resident_kernel", C.c_int32), ("tile_blocks_y", C.c_int32)]
 
 
 def sources():

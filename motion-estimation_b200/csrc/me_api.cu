@@ -203,7 +203,8 @@ int configure(me_ctx *c)
     const int forced_tmb = env_int("ME_TBX", 0), forced_pitch = env_int("ME_PITCH", 0);
     const int forced_nsx = env_int("ME_NSX", 0), forced_nsy = env_int("ME_NSY", 0);
     const long long work_enough = 32000;          // block-candidates per CTA beyond which a bigger CTA buys nothing
-    struct Plan { int nsx = 0, nsy = 0, su = 0, sd = 0, pitch = 0, tmb = 0, smem = 0, copy = 0, box_rows = 0, n_row_boxes = 0; long long work = 0; bool under = false; double balance = 0; };
+    const int forced_tmr = env_int("ME_TMR", 0);
+    struct Plan { int nsx = 0, nsy = 0, su = 0, sd = 0, pitch = 0, tmb = 0, tmr = 1, smem = 0, copy = 0, box_rows = 0, n_row_boxes = 0; long long work = 0; bool under = false; double balance = 0; };
     Plan best;
     for (int tsx = 1; tsx <= 8; ++tsx) {
         int su = tsx == 1 ? U : ((U / tsx) & ~15);
@@ -219,7 +220,12 @@ int configure(me_ctx *c)
             if (tsy > 1 && nsy != tsy) continue;
             if (forced_nsy && nsy != forced_nsy) continue;
             const int hmax = U - (nsy - 1) * sd;
-            const int win_rows = ceil_div(hmax, NDY) * NDY + B - 1;
+            // Block rows per tile: more than one only without slabs (a small range leaves little work per row,
+            // and the window's 2R halo rows are then shared by the rows of the tile).
+            for (int tmr = 1; tmr <= (nsx * nsy == 1 ? 8 : 1); ++tmr) {
+            if (forced_tmr && tmr != forced_tmr) continue;
+            if (tmr > 1 && (tmr > a.nby || tmr * B > 256)) break;
+            const int win_rows = ceil_div(hmax, NDY) * NDY + tmr * B - 1;
             const int n_row_boxes = ceil_div(win_rows, 256), box_rows = ceil_div(win_rows, n_row_boxes);
             const int alloc_rows = n_row_boxes * box_rows;
             for (int pi = 0; pi < 3; ++pi) {
@@ -228,30 +234,34 @@ int configure(me_ctx *c)
                 int tmb = (pitch - a.x_off - (wmax - 1)) / MB;
                 if (tmb > 256 / MB) tmb = 256 / MB;                 // reference strip is 256 bytes wide
                 if (tmb * NSUB > me::kMaxKeys) tmb = me::kMaxKeys / NSUB;
+                if (tmb * NSUB * tmr > me::kMaxTileKeys) tmb = me::kMaxTileKeys / (NSUB * tmr);
                 if (tmb > a.nmbx) tmb = a.nmbx;
                 if (forced_tmb) { if (forced_tmb > tmb) continue; tmb = forced_tmb; }
                 if (tmb < 1) continue;
                 // small frames: keep at least ~2 CTAs per SM in flight for a 4-pair batch
+                if (tmr > 1 && !forced_tmr &&
+                    (long long)ceil_div(a.nmbx, tmb) * ceil_div(a.nby, tmr) * (c->max_pairs > 4 ? 4 : c->max_pairs) < 2ll * c->sm_count) continue;
                 if (!forced_tmb)
-                    while (tmb > 1 && (long long)ceil_div(a.nmbx, tmb) * a.nby * nsx * nsy * (c->max_pairs > 4 ? 4 : c->max_pairs) < 2ll * c->sm_count) --tmb;
+                    while (tmb > 1 && (long long)ceil_div(a.nmbx, tmb) * ceil_div(a.nby, tmr) * nsx * nsy * (c->max_pairs > 4 ? 4 : c->max_pairs) < 2ll * c->sm_count) --tmb;
                 // every tile width from the widest that fits down to half of it: a narrower tile can
                 // divide its work items over the CTA's warps more evenly (r01: 8 blocks beat 9 by 1.2 %)
                 const int tmb_lo = forced_tmb ? tmb : (tmb + 1) / 2;
                 for (int t = tmb; t >= tmb_lo; --t) {
                     Plan p;
-                    p.nsx = nsx; p.nsy = nsy; p.su = su; p.sd = sd; p.pitch = pitch; p.tmb = t;
+                    p.nsx = nsx; p.nsy = nsy; p.su = su; p.sd = sd; p.pitch = pitch; p.tmb = t; p.tmr = tmr;
                     p.box_rows = box_rows; p.n_row_boxes = n_row_boxes;
                     p.copy = round_up(alloc_rows * pitch, 128);
-                    p.smem = a.n_bufs * p.copy + 128 + 256 + me::kRefPitch * B + me::kMaxKeys * 8 + 64;
+                    p.smem = a.n_bufs * p.copy + 128 + 256 + me::kRefPitch * B * tmr + me::kMaxTileKeys * 8 + 64;
                     if (p.smem < 20 * 1024) p.smem = 20 * 1024;          // the pair reduction's histograms live in the same memory
                     if (p.smem > 227 * 1024) continue;
                     p.under = p.smem <= smem_cap;
-                    p.work = (long long)t * NSUB * wmax * hmax;
+                    p.work = (long long)t * NSUB * tmr * wmax * hmax;
                     // work items of a full tile over 256 threads: fraction of warp passes that are full
                     const int nqw = ((wmax - 1) / 4 + 1) / NQ + 3 * (((wmax - 2) / 4 + 1) / NQ);   // ~ wide column groups
-                    const long long items = (long long)t * ceil_div(hmax, NDY) * (nqw > 0 ? nqw : 1);
+                    const long long items = (long long)t * tmr * ceil_div(hmax, NDY) * (nqw > 0 ? nqw : 1);
                     p.balance = (double)items / (double)(ceil_div((int)items, 256) * 256)
-                              * (double)a.nmbx / (double)(ceil_div(a.nmbx, t) * t);      // ... and of tiles that are full
+                              * (double)a.nmbx / (double)(ceil_div(a.nmbx, t) * t)       // ... and of tiles that are full
+                              * (double)a.nby / (double)(ceil_div(a.nby, tmr) * tmr);
                     const long long pw = p.work < work_enough ? p.work : work_enough, bw = best.work < work_enough ? best.work : work_enough;
                     bool better;
                     if (!best.tmb) better = true;
@@ -266,18 +276,24 @@ int configure(me_ctx *c)
                     if (better) best = p;
                 }
             }
+            }
         }
     }
     if (!best.tmb)
         return fail(ME_EUNSUPPORTED, "block %d with range %d: no slab of the candidate square fits one TMA box and 227 KB of "
                     "shared memory", B, R);
     a.nsx = best.nsx; a.nsy = best.nsy; a.su = best.su; a.sd = best.sd;
-    a.tmb = best.tmb; a.copy_bytes = best.copy; a.box_rows = best.box_rows; a.n_row_boxes = best.n_row_boxes;
+    a.tmb = best.tmb; a.tmr = best.tmr; a.copy_bytes = best.copy; a.box_rows = best.box_rows; a.n_row_boxes = best.n_row_boxes;
     c->win_pitch = best.pitch;
     c->smem = best.smem;
     c->kc = pick_kernel(B, best.pitch, k64);
     a.tiles_x = ceil_div(a.nmbx, a.tmb);
-    a.tiles_per_pair = a.tiles_x * a.nby;
+    a.tiles_per_pair = a.tiles_x * ceil_div(a.nby, a.tmr);
+    {
+        auto magic = [](int d) { return d <= 1 ? 0u : (unsigned)(0x100000000ull / (unsigned)d + 1ull); };
+        a.magic_nj[0] = magic(a.tmb);
+        a.magic_nj[1] = magic(a.nmbx - (a.tiles_x - 1) * a.tmb);
+    }
 
     // candidate tiling inside a slab of width w: per shift s the columns q with 4q + s < w, in NQ-wide
     // groups (16-byte aligned starts) plus single leftover columns.  Table 0: regular slab, 1: last slab.
@@ -325,6 +341,7 @@ int configure(me_ctx *c)
         const double t_prod = 6000.0 + (double)a.n_row_boxes * a.box_rows * (c->win_pitch / 16) / 32.0 * 120.0;
         if (a.nsx * a.nsy > 1 || t_cons < 2.7 * t_prod) c->smem_persistent = 0;
     }
+    if (a.tmr > 1) c->smem_persistent = 0;          // the resident kernel takes one block row per unit
 
     {   // fastdiv magics of full slabs (see sad_search.cuh)
         auto magic = [](int d) { return d <= 1 ? 0u : (unsigned)(0x100000000ull / (unsigned)d + 1ull); };
@@ -342,7 +359,7 @@ int configure(me_ctx *c)
 
     // Threads: whole multiples of 4 warps so that every scheduler of the SM gets the same number of warps
     // (r01 sweep: 224 threads = 7 warps ran 13 % slower than 128 or 256).
-    const int total = a.tmb * ceil_div(U - (a.nsy - 1) * a.sd, NDY) * a.n_wide[1];
+    const int total = a.tmb * a.tmr * ceil_div(U - (a.nsy - 1) * a.sd, NDY) * a.n_wide[1];
     c->threads = env_int("ME_THREADS", total >= 384 ? 256 : 128);
     if (c->threads % 32 || c->threads < 32 || c->threads > c->kc.maxt)
         return fail(ME_EINVAL, "ME_THREADS=%d is not a multiple of 32 in [32,%d]", c->threads, c->kc.maxt);
@@ -600,7 +617,7 @@ int me_create(int device, int height, int width, const me_params *params, int ma
     CREATE_TRY(cudaFuncSetAttribute(c->kc.fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
 #undef CREATE_TRY
     rc = make_tensor_map(&c->tm_win, c->d_frames, c->W, c->H, max_frames, c->pitch, c->win_pitch, c->args.box_rows);
-    if (!rc) rc = make_tensor_map(&c->tm_ref, c->d_frames, c->W, c->H, max_frames, c->pitch, me::kRefPitch, B);
+    if (!rc) rc = make_tensor_map(&c->tm_ref, c->d_frames, c->W, c->H, max_frames, c->pitch, me::kRefPitch, B * c->args.tmr);
     if (rc) { me_destroy(c); return rc; }
     *out = c;
     return ME_OK;
@@ -645,7 +662,7 @@ int me_get_geometry(const me_ctx *c, me_geometry *g)
     g->tiles_per_pair = c->args.tiles_per_pair;
     g->cand_px_per_pair = c->cand_px; g->cand_px_per_pair_valid = c->cand_px_valid;
     g->sm_count = c->sm_count; g->uses_tma = c->args.use_tma;
-    g->slabs_x = c->args.nsx; g->slabs_y = c->args.nsy; g->window_pitch = c->win_pitch; g->resident_kernel = c->smem_persistent ? 1 : 0;
+    g->slabs_x = c->args.nsx; g->slabs_y = c->args.nsy; g->window_pitch = c->win_pitch; g->resident_kernel = c->smem_persistent ? 1 : 0; g->tile_blocks_y = c->args.tmr;
     return ME_OK;
 }
 
@@ -850,7 +867,7 @@ int me_search_device(me_ctx *c, const uint8_t *d_frames, size_t pitch, int n_fra
     cudaStream_t st = stream ? (cudaStream_t)stream : c->s_compute;
     CUtensorMap tw, tr;
     rc = make_tensor_map(&tw, d_frames, c->W, c->H, n_frames, pitch, c->win_pitch, c->args.box_rows);
-    if (!rc) rc = make_tensor_map(&tr, d_frames, c->W, c->H, n_frames, pitch, me::kRefPitch, c->p.block);
+    if (!rc) rc = make_tensor_map(&tr, d_frames, c->W, c->H, n_frames, pitch, me::kRefPitch, c->p.block * c->args.tmr);
     if (rc) return rc;
     if (c->have_search) CU_TRY(cudaEventSynchronize(c->ev_search));
     memcpy(c->h_pairs, pairs, sizeof(int32_t) * 2 * (size_t)n_pairs);
@@ -1100,7 +1117,7 @@ extern "C" int me_search_static_scratch(const uint8_t *d_frames, size_t pitch, i
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     CUtensorMap tw, tr;
     rc = make_tensor_map(&tw, d_frames, width, height, n_frames, pitch, plan.win_pitch, plan.args.box_rows);
-    if (!rc) rc = make_tensor_map(&tr, d_frames, width, height, n_frames, pitch, me::kRefPitch, B);
+    if (!rc) rc = make_tensor_map(&tr, d_frames, width, height, n_frames, pitch, me::kRefPitch, B * plan.args.tmr);
     if (rc) return rc;
     CU_TRY(cudaFuncSetAttribute(plan.kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, plan.smem));
     CU_TRY(cudaFuncSetAttribute(plan.kc.fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));

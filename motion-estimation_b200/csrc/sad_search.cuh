@@ -34,7 +34,8 @@
 
 namespace me {
 
-constexpr int kMaxKeys = 32;          // blocks per tile
+constexpr int kMaxKeys = 32;          // blocks per tile row
+constexpr int kMaxTileKeys = 128;     // blocks per tile of the one-CTA-per-tile kernel (tmr rows of up to kMaxKeys)
 constexpr int kMaxGroups = 96;        // column groups per block (wide + narrow)
 constexpr int kRefPitch = 256;        // bytes per row of the reference strip in shared memory
 constexpr unsigned kFull = 0xffffffffu;
@@ -58,7 +59,9 @@ struct SearchArgs {
     // block grid
     int nbx, nby, nb;
     int R, U;                   // U = 2R + 1
-    int tmb, tiles_x, tiles_per_pair;   // macro-blocks per tile
+    int tmb, tiles_x, tiles_per_pair;   // macro-blocks per tile row
+    int tmr;                    // block rows per tile (> 1 only for single-slab plans with little work per row: small ranges)
+    unsigned magic_nj[2];       // fastdiv by the macro-blocks of a tile row, [last tile in x]
     int nmbx;                   // macro-blocks per frame row = ceil(nbx / NSUB)
     // shared-memory window: 4 shifted copies, each alloc_rows x PITCH bytes
     int copy_bytes;
@@ -432,7 +435,7 @@ template <int B, int NDY, int NQP, int PITCH, int LW, bool K64, int RB>
 __device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j, int dyg, int s, int q0,
                                          const uint8_t *s_win, const uint8_t *s_ref,
                                          typename KeyOf<K64>::T *s_key, bool tile_interior, int dyi_lo, int dyi_hi,
-                                         int X0, int lane, int ubase, int dbase, int slab_w)
+                                         int X0, int lane, int ubase, int dbase, int slab_w, int jy = 0, int key_row = 0)
 {
     using KeyT = typename KeyOf<K64>::T;
     using G = Geo<B>;
@@ -454,8 +457,8 @@ __device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j
 #pragma unroll
                 for (int q = 0; q < NQP; ++q) acc[sb][d][q] = 0;
         const uint32_t *cur = reinterpret_cast<const uint32_t *>(s_win + (size_t)s * (a.copy_bytes + kCopySkew)) +
-                              dyg * NDY * (PITCH / 4) + j * G::BW + q0;
-        const uint32_t *ref = reinterpret_cast<const uint32_t *>(s_ref) + j * G::BW;
+                              (dyg * NDY + jy * B) * (PITCH / 4) + j * G::BW + q0;
+        const uint32_t *ref = reinterpret_cast<const uint32_t *>(s_ref) + jy * B * (kRefPitch / 4) + j * G::BW;
         sad_patch<B, NDY, NQP, PITCH, LW>(cur, ref, acc);
 
         // everything below is in SLAB-LOCAL index space: u = dx + R - ubase, dyi = dy + R - dbase
@@ -509,15 +512,16 @@ __device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j
         }
     }
     // block-level argmin: one shared atomic per warp when the warp sits in one macro-block
-    const int j0 = __shfl_sync(kFull, j, 0);
-    const bool uniform = __all_sync(kFull, j == j0);
+    const int kj = key_row + j;                                         // macro-block slot in the tile's key table
+    const int j0 = __shfl_sync(kFull, kj, 0);
+    const bool uniform = __all_sync(kFull, kj == j0);
 #pragma unroll
     for (int sb = 0; sb < G::NSUB; ++sb) {
         if (uniform) {
             const KeyT m = warp_min_key(best[sb]);
             if (lane == 0 && m != kNone) atomicMin(&s_key[j0 * G::NSUB + sb], m);
         } else if (best[sb] != kNone) {
-            atomicMin(&s_key[j * G::NSUB + sb], best[sb]);
+            atomicMin(&s_key[kj * G::NSUB + sb], best[sb]);
         }
     }
 }
@@ -545,29 +549,33 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     const int lastx = sx == a.nsx - 1;
     const int slab_w = lastx ? a.U - ubase : a.su, slab_h = (sy == a.nsy - 1) ? a.U - dbase : a.sd;
     const int prev_slot = __ldg(a.pairs + 2 * pair), cur_slot = __ldg(a.pairs + 2 * pair + 1);
-    const int X0 = tx * a.tmb * G::MB, Y0 = ty * B;
-    const int nj = min(a.tmb, a.nmbx - tx * a.tmb);                    // macro-blocks in this tile
-    const int nblk = min(nj * G::NSUB, a.nbx - tx * a.tmb * G::NSUB);  // blocks in this tile
+    const int X0 = tx * a.tmb * G::MB, Y0 = ty * a.tmr * B;
+    const int nj = min(a.tmb, a.nmbx - tx * a.tmb);                    // macro-blocks in a row of this tile
+    const int nblk = min(nj * G::NSUB, a.nbx - tx * a.tmb * G::NSUB);  // blocks in a row of this tile
+    const int nrows = min(a.tmr, a.nby - ty * a.tmr);                  // block rows in this tile
 
     uint8_t *s_win = smem;                                            // 4 shifted copies
     uint8_t *s_raw = a.x_off ? smem + 4 * (size_t)a.copy_bytes + 128 : smem;   // TMA destination (128-byte aligned)
     uint8_t *s_ref = smem + (size_t)a.n_bufs * a.copy_bytes + 128 + 256;       // copy skews + 256 B of slack for tile over-reads
-    constexpr int ref_bytes = kRefPitch * B;
-    KeyT *s_key = reinterpret_cast<KeyT *>(s_ref + ref_bytes);         // [kMaxKeys]
-    uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_ref + ref_bytes + kMaxKeys * 8);
+    const int ref_bytes = kRefPitch * B * a.tmr;
+    KeyT *s_key = reinterpret_cast<KeyT *>(s_ref + ref_bytes);         // [tmr][tmb * NSUB] <= kMaxTileKeys
+    uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_ref + ref_bytes + kMaxTileKeys * 8);
     int *s_last = reinterpret_cast<int *>(s_bar + 1);
 
     // ---- this slab's share of the block row's domain, in slab-local index space.  dy groups that lie wholly
     //      outside it are not enumerated at all (most of the work on the 64-pixel-tall recordings), and a slab
     //      with none loads nothing.
+    //      A tile of several block rows enumerates the union of its rows' ranges (the last row reaches furthest
+    //      up, the first furthest down); each item then tests against its own row.
     const int twoR = 2 * a.R;
-    const int dyi_lo = max(0, a.R - Y0 - dbase), dyi_hi = min(slab_h - 1, min(twoR, a.R + a.H - B - Y0) - dbase);
+    const int Ylast = Y0 + (nrows - 1) * B;
+    const int dyi_lo = max(0, a.R - Ylast - dbase), dyi_hi = min(slab_h - 1, min(twoR, a.R + a.H - B - Y0) - dbase);
     const int xlast = X0 + (nblk - 1) * B;
-    const bool tile_interior = dyi_lo == 0 && dyi_hi == slab_h - 1 && a.R - X0 - ubase <= 0 &&
-                               min(twoR, a.R + a.W - B - xlast) - ubase >= slab_w - 1;
+    const bool x_interior = a.R - X0 - ubase <= 0 && min(twoR, a.R + a.W - B - xlast) - ubase >= slab_w - 1;
+    const bool tile_interior = x_interior && a.R - Y0 - dbase <= 0 && min(twoR, a.R + a.H - B - Ylast) - dbase >= slab_h - 1;
     const int dyg_lo = dyi_lo / NDY, dyg_hi = dyi_hi >= 0 ? dyi_hi / NDY : -1;
     const int nd = dyi_hi >= dyi_lo ? dyg_hi - dyg_lo + 1 : 0;         // 0: this slab holds no candidate of this block row
-    if (tid < kMaxKeys) s_key[tid] = kNone;
+    if (tid < kMaxTileKeys) s_key[tid] = kNone;
 
     const int wx0 = X0 - a.R - a.x_off + ubase, wy0 = Y0 - a.R + dbase;   // wx0 is a multiple of 16 (su is)
     if (nd == 0) {
@@ -599,7 +607,7 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
         for (int i = tid; i < ref_bytes; i += blockDim.x) {
             const int r = i / kRefPitch, c = i - r * kRefPitch;
             const int gx = X0 + c, gy = Y0 + r;
-            s_ref[i] = (gx < a.W && gy < a.H) ? prevf[(size_t)gy * a.frame_pitch + gx] : 0;
+            s_ref[i] = (gx < a.W && gy < a.H) ? prevf[(size_t)gy * a.frame_pitch + gx] : 0;   // r runs over all tmr block rows
         }
         __syncthreads();
     }
@@ -655,38 +663,63 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     const bool usual = nd == a.full_nd[lasty];
     const unsigned short *grp = a.group[lastx];
     const int n_wide = a.n_wide[lastx], n_narrow = a.n_narrow[lastx];
+    const int njt = nj * nrows;                                        // macro-blocks in the tile, row-major
+    const unsigned magic_row = a.magic_nj[tx == a.tiles_x - 1];
+    const int key_stride = a.tmb;                                      // macro-block slots per row of s_key
+    // row of macro-block jj, and that row's own share of the dy domain
+    auto row_domain = [&](int jj, int dyg, bool &act, int &jx, int &jy, int &lo, int &hi, bool &inter) {
+        jy = fastdiv(jj, magic_row); jx = jj - jy * nj;
+        const int y0r = Y0 + jy * B;
+        lo = max(0, a.R - y0r - dbase); hi = min(slab_h - 1, min(twoR, a.R + a.H - B - y0r) - dbase);
+        inter = x_interior && lo == 0 && hi == slab_h - 1;
+        act = act && dyg * NDY + NDY - 1 >= lo && dyg * NDY <= hi;      // a dy group wholly outside this row's range: nothing to do
+    };
     for (int rep = 0; rep < a.repeat; ++rep) {
     if (nd > 0) {   // wide patches: NDY x NQ
         const int per_j = nd * n_wide;
-        const int total = nj * per_j;
+        const int total = njt * per_j;
         const unsigned magic_pj = usual ? a.magic_wide[lasty][lastx] : fastdiv_magic((unsigned)per_j);
         const int iters = (total + (int)blockDim.x - 1) / (int)blockDim.x;
         for (int it = 0; it < iters; ++it) {
             const int w_raw = it * (int)blockDim.x + tid;
-            const bool active = w_raw < total;
+            bool active = w_raw < total;
             const int w = active ? w_raw : total - 1;
             const int j = fastdiv(w, magic_pj), r = w - j * per_j;
             const int dq = fastdiv(r, a.magic_nw[lastx]), cg = r - dq * n_wide, dyg = dyg_lo + dq;   // column group varies fastest across lanes
             const unsigned g = grp[cg];
-            run_item<B, NDY, NQ, PITCH, LWW, K64, RB>(a, active, j, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
-                                                      s_key, tile_interior, dyi_lo, dyi_hi, X0, lane, ubase, dbase, slab_w);
+            if (a.tmr == 1) {
+                run_item<B, NDY, NQ, PITCH, LWW, K64, RB>(a, active, j, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
+                                                          s_key, tile_interior, dyi_lo, dyi_hi, X0, lane, ubase, dbase, slab_w);
+            } else {
+                int jx, jy, lo, hi; bool inter;
+                row_domain(j, dyg, active, jx, jy, lo, hi, inter);
+                run_item<B, NDY, NQ, PITCH, LWW, K64, RB>(a, active, jx, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
+                                                          s_key, inter, lo, hi, X0, lane, ubase, dbase, slab_w, jy, jy * key_stride);
+            }
         }
     }
     if (nd > 0 && n_narrow > 0) {   // leftover columns: NDY x 1
         const int per_j = nd * n_narrow;
-        const int total = nj * per_j;
+        const int total = njt * per_j;
         const unsigned magic_pj = usual ? a.magic_narrow[lasty][lastx] : fastdiv_magic((unsigned)per_j);
         const int iters = (total + (int)blockDim.x - 1) / (int)blockDim.x;
         for (int it = 0; it < iters; ++it) {
             // handed out from the LAST warp down: the first warps carry the extra wide pass of a ragged tile
             const int w_raw = it * (int)blockDim.x + ((int)blockDim.x - 1 - tid);
-            const bool active = w_raw < total;
+            bool active = w_raw < total;
             const int w = active ? w_raw : total - 1;
             const int j = fastdiv(w, magic_pj), r = w - j * per_j;
             const int dq = fastdiv(r, a.magic_nn[lastx]), cg = r - dq * n_narrow, dyg = dyg_lo + dq;
             const unsigned g = grp[n_wide + cg];
-            run_item<B, NDY, 1, PITCH, 1, K64, RB>(a, active, j, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
-                                                   s_key, tile_interior, dyi_lo, dyi_hi, X0, lane, ubase, dbase, slab_w);
+            if (a.tmr == 1) {
+                run_item<B, NDY, 1, PITCH, 1, K64, RB>(a, active, j, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
+                                                       s_key, tile_interior, dyi_lo, dyi_hi, X0, lane, ubase, dbase, slab_w);
+            } else {
+                int jx, jy, lo, hi; bool inter;
+                row_domain(j, dyg, active, jx, jy, lo, hi, inter);
+                run_item<B, NDY, 1, PITCH, 1, K64, RB>(a, active, jx, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
+                                                       s_key, inter, lo, hi, X0, lane, ubase, dbase, slab_w, jy, jy * key_stride);
+            }
         }
     }
     }
@@ -722,9 +755,10 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
         constexpr KeyT rmask = (KeyT(1) << RB) - 1;
         constexpr int per_warp = 32 / kFinLanes;
         const int grp = lane / kFinLanes;
-        for (int jb = warp * per_warp + grp; jb < nblk; jb += nwarps * per_warp) {
-            const KeyT key = s_key[jb];
-            finalize_block<B>(a, pair, prevf, curf, tx * a.tmb * G::NSUB + jb, ty, (uint32_t)(key >> RB),
+        for (int jt = warp * per_warp + grp; jt < nblk * nrows; jt += nwarps * per_warp) {
+            const int jr = jt / nblk, jb = jt - jr * nblk;             // block row in the tile, block in the row
+            const KeyT key = s_key[jr * a.tmb * G::NSUB + jb];
+            finalize_block<B>(a, pair, prevf, curf, tx * a.tmb * G::NSUB + jb, ty * a.tmr + jr, (uint32_t)(key >> RB),
                               (uint32_t)(key & rmask), lane % kFinLanes, ((1u << kFinLanes) - 1u) << (grp * kFinLanes));
         }
     }

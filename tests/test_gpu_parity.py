@@ -131,6 +131,25 @@ def test_tile_width_does_not_change_results(me, monkeypatch, tbx):
         check_pair(est, 0, frames[0], frames[1], cfg, res[0])
 
 
+@pytest.mark.parametrize("B,R,tmr,H,W", [(16, 8, 2, 112, 240), (16, 8, 3, 112, 240), (16, 6, 4, 120, 208), (8, 5, 4, 88, 200),
+                                         (8, 12, 5, 88, 200), (32, 9, 2, 160, 224), (16, 16, 7, 112, 144), (16, 20, 2, 64, 640)])
+def test_tile_height_does_not_change_results(me, monkeypatch, B, R, tmr, H, W):
+    """Tiles of several block rows (the plan for small ranges): rows at the top and bottom of the frame have
+    their own, smaller dy range; the last tile row is ragged for most of these shapes."""
+    from motion_estimation_b200 import synth
+    frames, _ = synth.translating_frames(3, H, W, min(R, 12))
+    cfg = me.SearchConfig(block=B, range=R)
+    monkeypatch.setenv("ME_TMR", str(tmr))
+    with me.MotionEstimator(H, W, cfg, max_frames=3, max_pairs=3) as est:
+        assert est.geometry["tile_blocks_y"] == tmr
+        est.upload(frames)
+        pairs = [(0, 1), (1, 2), (2, 0)]
+        for _ in range(2):
+            res = est.search(pairs)
+            for i, (a, c) in enumerate(pairs):
+                check_pair(est, i, frames[a], frames[c], cfg, res[i])
+
+
 def test_example_recordings_equal_oracle(me, golden_clips):
     """Every example sequence: integer displacements bit-exact against the oracle (north_star)."""
     cfg = me.SearchConfig(block=16, range=32)
