@@ -7,14 +7,14 @@ from motion_estimation_b200 import synth
 PEAK = 74.4e12
 rows = []
 for (H, W) in ((720, 1280), (1080, 1920), (2160, 3840)):
-    base, _ = synth.translating_frames(3, H, W, 8)
+    base, _ = synth.translating_frames(65, H, W, 8)
     for B in (8, 16, 32):
         for R in (8, 16, 32, 64, 128):
-            P = 2
+            P = int(max(2, min(64, round(2e11 / ((W // B) * (H // B) * B * B * (2 * R + 1) ** 2)))))   # ~3 ms launches
             try:
-                with me.MotionEstimator(H, W, me.SearchConfig(block=B, range=R), max_frames=3, max_pairs=P) as est:
-                    est.upload(base)
-                    pairs = [(0, 1), (1, 2)]
+                with me.MotionEstimator(H, W, me.SearchConfig(block=B, range=R), max_frames=P + 1, max_pairs=P) as est:
+                    est.upload(base[:P + 1])
+                    pairs = [(k, k + 1) for k in range(P)]
                     est.search(pairs)
                     ms = []
                     for _ in range(2):
@@ -22,7 +22,7 @@ for (H, W) in ((720, 1280), (1080, 1920), (2160, 3840)):
                     g = est.geometry
                     t = min(ms) * 1e-3
                     rows.append((W, H, B, R, P / t, g["cand_px_per_pair_valid"] * P / t / 1e12, g["cand_px_per_pair_valid"] * P / t / PEAK,
-                                 g["tile_blocks_x"], g["threads_per_cta"], g["smem_bytes"], g["slabs_x"], g["slabs_y"], g["window_pitch"]))
+                                 P, g["tile_blocks_x"], g["tile_blocks_y"], g["resident_kernel"], g["threads_per_cta"], g["smem_bytes"], g["slabs_x"], g["slabs_y"], g["window_pitch"]))
             except me.MEError as e:
                 rows.append((W, H, B, R, 0, 0, 0, str(e)))
             r = rows[-1]
