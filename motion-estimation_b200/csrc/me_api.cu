@@ -83,7 +83,7 @@ int make_tensor_map(CUtensorMap *tm, const uint8_t *base, int W, int H, int n_fr
 struct KernelChoice {
     const void *fn = nullptr;
     const void *fn_persistent = nullptr;   // warp-specialised resident form (32-bit keys only)
-    int ndy = 0, nq = 0, maxt = 0, pitch = 0, rank_bits = 0;
+    int ndy = 0, nq = 0, maxt = 0, pitch = 0, rank_bits = 0, persist_threads = 0;
 };
 
 constexpr int kNDY = 5, kNQ = 4, kMaxThreads = 256;
@@ -94,7 +94,11 @@ KernelChoice choice()
 {
     KernelChoice k;
     k.fn = (const void *)&me::sad_search_kernel<B, kNDY, kNQ, PITCH, K64, RB, kMaxThreads, 3>;
-    if constexpr (!K64 && B <= 16) k.fn_persistent = (const void *)&me::sad_search_persistent<B, kNDY, kNQ, PITCH, K64, RB>;
+    if constexpr (!K64) {
+        constexpr int CW = B <= 16 ? me::kConsumerWarps : me::kConsumerWarps32;
+        k.fn_persistent = (const void *)&me::sad_search_persistent<B, kNDY, kNQ, PITCH, K64, RB, CW>;
+        k.persist_threads = 32 * (1 + CW);
+    }
     k.ndy = kNDY; k.nq = kNQ; k.maxt = kMaxThreads; k.pitch = PITCH; k.rank_bits = RB;
     return k;
 }
@@ -399,7 +403,7 @@ int launch_search(me_ctx *c, const uint8_t *frames, const CUtensorMap &tm_win, c
         CU_TRY(cudaMemsetAsync(c->d_ready, 0xff, sizeof(int) * (size_t)(n_pairs + 1), st));
         void *params[4] = {(void *)&tm_win, (void *)&tm_ref, (void *)&a, (void *)&pa};
         const unsigned grid = units < c->sm_count ? (unsigned)units : (unsigned)c->sm_count;
-        CU_TRY(cudaLaunchKernel(c->kc.fn_persistent, dim3(grid), dim3((unsigned)me::kPersistThreads), params,
+        CU_TRY(cudaLaunchKernel(c->kc.fn_persistent, dim3(grid), dim3((unsigned)c->kc.persist_threads), params,
                                 (size_t)c->smem_persistent, st));
     } else {
         void *params[3] = {(void *)&tm_win, (void *)&tm_ref, (void *)&a};

@@ -24,7 +24,8 @@
 namespace me {
 
 constexpr int kStages = 2;
-constexpr int kConsumerWarps = 20;
+constexpr int kConsumerWarps = 20;        // 8/16-pixel blocks (80 registers per thread)
+constexpr int kConsumerWarps32 = 16;      // 32-pixel blocks: the patch needs ~110 registers
 constexpr int kPersistThreads = 32 * (1 + kConsumerWarps);
 
 struct UnitInfo {                  // one per stage: written by the producer, read by the consumers
@@ -183,8 +184,8 @@ __device__ __forceinline__ void close_unit(const SearchArgs &a, const PersistArg
     }
 }
 
-template <int B, int NDY, int NQ, int PITCH, bool K64, int RB>
-__global__ void __launch_bounds__(kPersistThreads, 1)
+template <int B, int NDY, int NQ, int PITCH, bool K64, int RB, int CW>
+__global__ void __launch_bounds__(32 * (1 + CW), 1)
 sad_search_persistent(const __grid_constant__ CUtensorMap tm_win, const __grid_constant__ CUtensorMap tm_ref,
                       const SearchArgs a, const PersistArgs pa)
 {
@@ -210,7 +211,7 @@ sad_search_persistent(const __grid_constant__ CUtensorMap tm_win, const __grid_c
         for (int s = 0; s < kStages; ++s) {
             mbar_init_only(&bars[s], 1);                       // full: one arrive.expect_tx + the TMA bytes
             mbar_init_only(&bars[2 + s], 1);                   // ready: the producer
-            mbar_init_only(&bars[4 + s], kConsumerWarps);      // empty: every consumer warp
+            mbar_init_only(&bars[4 + s], CW);                  // empty: every consumer warp
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }

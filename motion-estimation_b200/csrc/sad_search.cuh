@@ -156,9 +156,9 @@ __device__ __forceinline__ unsigned long long warp_min_key(unsigned long long v)
 //   cur : word pointer to copy s, window row dyi0, word j*BW + q0
 //   ref : word pointer to the reference strip, row 0, word j*BW
 // LW = words per shared load of the current-frame row (4 needs j*BW + q0 to be a multiple of 4).
-template <int B, int NDY, int NQP, int PITCH, int LW>
-__device__ __forceinline__ void sad_patch(const uint32_t *__restrict__ cur, const uint32_t *__restrict__ ref,
-                                          uint32_t (&acc)[Geo<B>::NSUB][NDY][NQP])
+template <int B, int ROWS, int NDY, int NQP, int PITCH, int LW>
+__device__ __forceinline__ void sad_rows(const uint32_t *__restrict__ cur, const uint32_t *__restrict__ ref,
+                                         uint32_t (&acc)[Geo<B>::NSUB][NDY][NQP])
 {
     constexpr int BW = Geo<B>::BW, SW = Geo<B>::SW;
     constexpr int PW = PITCH / 4, RPW = kRefPitch / 4;
@@ -166,7 +166,7 @@ __device__ __forceinline__ void sad_patch(const uint32_t *__restrict__ cur, cons
     constexpr int NLD = (NCW + LW - 1) / LW;
     uint32_t refw[NDY][BW];                         // rotating window of the last NDY reference rows
 #pragma unroll
-    for (int yy = 0; yy < B + NDY - 1; ++yy) {
+    for (int yy = 0; yy < ROWS + NDY - 1; ++yy) {
         uint32_t cw[NLD * LW];
         const uint32_t *crow = cur + yy * PW;
 #pragma unroll
@@ -178,7 +178,7 @@ __device__ __forceinline__ void sad_patch(const uint32_t *__restrict__ cur, cons
                 cw[l] = crow[l];
             }
         }
-        if (yy < B) {
+        if (yy < ROWS) {
             const uint32_t *rrow = ref + yy * RPW;
 #pragma unroll
             for (int l = 0; l < BW / 4; ++l) {
@@ -190,7 +190,7 @@ __device__ __forceinline__ void sad_patch(const uint32_t *__restrict__ cur, cons
 #pragma unroll
         for (int d = 0; d < NDY; ++d) {
             const int i = yy - d;                   // reference row paired with this window row for dy index d
-            if (i >= 0 && i < B) {
+            if (i >= 0 && i < ROWS) {
 #pragma unroll
                 for (int w = 0; w < BW; ++w)
 #pragma unroll
@@ -198,6 +198,31 @@ __device__ __forceinline__ void sad_patch(const uint32_t *__restrict__ cur, cons
                         acc[w / SW][d][q] = vsad4(refw[i % NDY][w], cw[q + w], acc[w / SW][d][q]);
             }
         }
+    }
+}
+
+// A 32-row block runs as four 8-row slices through the same (rolled) body of 1280 SAD ops, the size of the
+// 16x16 patch: the fully unrolled 36-row form is 80 KB of straight-line code and starved the warps of
+// instructions (r01e ncu: 1.9 no-instruction stalls per issue, still 1.0 with two 16-row halves); the price
+// is 4 extra window rows of loads per slice.
+#ifndef ME_SLICE16
+#define ME_SLICE16 0
+#endif
+constexpr bool kSlice16 = ME_SLICE16 != 0;       // experiment: 16-row blocks as two rolled 8-row slices
+template <int B, int NDY, int NQP, int PITCH, int LW>
+__device__ __forceinline__ void sad_patch(const uint32_t *__restrict__ cur, const uint32_t *__restrict__ ref,
+                                          uint32_t (&acc)[Geo<B>::NSUB][NDY][NQP])
+{
+    if constexpr (B == 32) {
+#pragma unroll 1
+        for (int part = 0; part < 4; ++part)
+            sad_rows<B, 8, NDY, NQP, PITCH, LW>(cur + part * 8 * (PITCH / 4), ref + part * 8 * (kRefPitch / 4), acc);
+    } else if constexpr (B == 16 && kSlice16) {
+#pragma unroll 1
+        for (int part = 0; part < 2; ++part)
+            sad_rows<B, 8, NDY, NQP, PITCH, LW>(cur + part * 8 * (PITCH / 4), ref + part * 8 * (kRefPitch / 4), acc);
+    } else {
+        sad_rows<B, B, NDY, NQP, PITCH, LW>(cur, ref, acc);
     }
 }
 
