@@ -56,7 +56,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and os.path.exists(SO_PATH) and all(os.path.getmtime(SO_PATH) >= os.path.getmtime(s) for s in srcs):
         return SO_PATH
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO_PATH, srcs[0]]
+    extra = os.environ.get("ME_NVCC_EXTRA", "").split()             # experiments only, e.g. -DME_SLICE16=1
+    cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO_PATH, srcs[0]]
     env = dict(os.environ)
     env.pop("CC", None)
     env.pop("CXX", None)

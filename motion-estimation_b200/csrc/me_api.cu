@@ -82,6 +82,7 @@ int make_tensor_map(CUtensorMap *tm, const uint8_t *base, int W, int H, int n_fr
 
 struct KernelChoice {
     const void *fn = nullptr;
+    const void *fn_multirow = nullptr;     // the same kernel for tiles of several block rows
     const void *fn_persistent = nullptr;   // warp-specialised resident form (32-bit keys only)
     int ndy = 0, nq = 0, maxt = 0, pitch = 0, rank_bits = 0, persist_threads = 0;
 };
@@ -93,7 +94,8 @@ template <int B, int PITCH, bool K64, int RB>
 KernelChoice choice()
 {
     KernelChoice k;
-    k.fn = (const void *)&me::sad_search_kernel<B, kNDY, kNQ, PITCH, K64, RB, kMaxThreads, 3>;
+    k.fn = (const void *)&me::sad_search_kernel<B, kNDY, kNQ, PITCH, K64, RB, kMaxThreads, 3, false>;
+    k.fn_multirow = (const void *)&me::sad_search_kernel<B, kNDY, kNQ, PITCH, K64, RB, kMaxThreads, 3, true>;
     if constexpr (!K64) {
         constexpr int CW = B <= 16 ? me::kConsumerWarps : me::kConsumerWarps32;
         k.fn_persistent = (const void *)&me::sad_search_persistent<B, kNDY, kNQ, PITCH, K64, RB, CW>;
@@ -291,6 +293,7 @@ int configure(me_ctx *c)
     c->win_pitch = best.pitch;
     c->smem = best.smem;
     c->kc = pick_kernel(B, best.pitch, k64);
+    if (best.tmr > 1) c->kc.fn = c->kc.fn_multirow;
     a.tiles_x = ceil_div(a.nmbx, a.tmb);
     a.tiles_per_pair = a.tiles_x * ceil_div(a.nby, a.tmr);
     {

@@ -205,10 +205,6 @@ __device__ __forceinline__ void sad_rows(const uint32_t *__restrict__ cur, const
 // 16x16 patch: the fully unrolled 36-row form is 80 KB of straight-line code and starved the warps of
 // instructions (r01e ncu: 1.9 no-instruction stalls per issue, still 1.0 with two 16-row halves); the price
 // is 4 extra window rows of loads per slice.
-#ifndef ME_SLICE16
-#define ME_SLICE16 0
-#endif
-constexpr bool kSlice16 = ME_SLICE16 != 0;       // experiment: 16-row blocks as two rolled 8-row slices
 template <int B, int NDY, int NQP, int PITCH, int LW>
 __device__ __forceinline__ void sad_patch(const uint32_t *__restrict__ cur, const uint32_t *__restrict__ ref,
                                           uint32_t (&acc)[Geo<B>::NSUB][NDY][NQP])
@@ -217,11 +213,7 @@ __device__ __forceinline__ void sad_patch(const uint32_t *__restrict__ cur, cons
 #pragma unroll 1
         for (int part = 0; part < 4; ++part)
             sad_rows<B, 8, NDY, NQP, PITCH, LW>(cur + part * 8 * (PITCH / 4), ref + part * 8 * (kRefPitch / 4), acc);
-    } else if constexpr (B == 16 && kSlice16) {
-#pragma unroll 1
-        for (int part = 0; part < 2; ++part)
-            sad_rows<B, 8, NDY, NQP, PITCH, LW>(cur + part * 8 * (PITCH / 4), ref + part * 8 * (kRefPitch / 4), acc);
-    } else {
+    } else {                                        // 16 rows as two slices measured slower (0.854 vs 0.867): the extra loads cost more
         sad_rows<B, B, NDY, NQP, PITCH, LW>(cur, ref, acc);
     }
 }
@@ -552,7 +544,9 @@ __device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j
 }
 
 // ---------------------------------------------------------------- the search kernel
-template <int B, int NDY, int NQ, int PITCH, bool K64, int RB, int MAXT, int MINB>
+// MR = tiles of several block rows (a.tmr > 1).  A separate instantiation: carrying the row arithmetic in the
+// one-row kernel cost it 3 % (r01e: 0.846 -> 0.819 at 1080p/16/+-32).
+template <int B, int NDY, int NQ, int PITCH, bool K64, int RB, int MAXT, int MINB, bool MR>
 __global__ void __launch_bounds__(MAXT, MINB)
 sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_constant__ CUtensorMap tm_ref,
                   const SearchArgs a)
@@ -574,15 +568,16 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     const int lastx = sx == a.nsx - 1;
     const int slab_w = lastx ? a.U - ubase : a.su, slab_h = (sy == a.nsy - 1) ? a.U - dbase : a.sd;
     const int prev_slot = __ldg(a.pairs + 2 * pair), cur_slot = __ldg(a.pairs + 2 * pair + 1);
-    const int X0 = tx * a.tmb * G::MB, Y0 = ty * a.tmr * B;
+    const int tmr = MR ? a.tmr : 1;
+    const int X0 = tx * a.tmb * G::MB, Y0 = ty * tmr * B;
     const int nj = min(a.tmb, a.nmbx - tx * a.tmb);                    // macro-blocks in a row of this tile
     const int nblk = min(nj * G::NSUB, a.nbx - tx * a.tmb * G::NSUB);  // blocks in a row of this tile
-    const int nrows = min(a.tmr, a.nby - ty * a.tmr);                  // block rows in this tile
+    const int nrows = MR ? min(tmr, a.nby - ty * tmr) : 1;             // block rows in this tile
 
     uint8_t *s_win = smem;                                            // 4 shifted copies
     uint8_t *s_raw = a.x_off ? smem + 4 * (size_t)a.copy_bytes + 128 : smem;   // TMA destination (128-byte aligned)
     uint8_t *s_ref = smem + (size_t)a.n_bufs * a.copy_bytes + 128 + 256;       // copy skews + 256 B of slack for tile over-reads
-    const int ref_bytes = kRefPitch * B * a.tmr;
+    const int ref_bytes = kRefPitch * B * tmr;
     KeyT *s_key = reinterpret_cast<KeyT *>(s_ref + ref_bytes);         // [tmr][tmb * NSUB] <= kMaxTileKeys
     uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_ref + ref_bytes + kMaxTileKeys * 8);
     int *s_last = reinterpret_cast<int *>(s_bar + 1);
@@ -712,14 +707,14 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
             const int j = fastdiv(w, magic_pj), r = w - j * per_j;
             const int dq = fastdiv(r, a.magic_nw[lastx]), cg = r - dq * n_wide, dyg = dyg_lo + dq;   // column group varies fastest across lanes
             const unsigned g = grp[cg];
-            if (a.tmr == 1) {
-                run_item<B, NDY, NQ, PITCH, LWW, K64, RB>(a, active, j, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
-                                                          s_key, tile_interior, dyi_lo, dyi_hi, X0, lane, ubase, dbase, slab_w);
-            } else {
+            if constexpr (MR) {
                 int jx, jy, lo, hi; bool inter;
                 row_domain(j, dyg, active, jx, jy, lo, hi, inter);
                 run_item<B, NDY, NQ, PITCH, LWW, K64, RB>(a, active, jx, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
                                                           s_key, inter, lo, hi, X0, lane, ubase, dbase, slab_w, jy, jy * key_stride);
+            } else {
+                run_item<B, NDY, NQ, PITCH, LWW, K64, RB>(a, active, j, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
+                                                          s_key, tile_interior, dyi_lo, dyi_hi, X0, lane, ubase, dbase, slab_w);
             }
         }
     }
@@ -736,14 +731,14 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
             const int j = fastdiv(w, magic_pj), r = w - j * per_j;
             const int dq = fastdiv(r, a.magic_nn[lastx]), cg = r - dq * n_narrow, dyg = dyg_lo + dq;
             const unsigned g = grp[n_wide + cg];
-            if (a.tmr == 1) {
-                run_item<B, NDY, 1, PITCH, 1, K64, RB>(a, active, j, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
-                                                       s_key, tile_interior, dyi_lo, dyi_hi, X0, lane, ubase, dbase, slab_w);
-            } else {
+            if constexpr (MR) {
                 int jx, jy, lo, hi; bool inter;
                 row_domain(j, dyg, active, jx, jy, lo, hi, inter);
                 run_item<B, NDY, 1, PITCH, 1, K64, RB>(a, active, jx, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
                                                        s_key, inter, lo, hi, X0, lane, ubase, dbase, slab_w, jy, jy * key_stride);
+            } else {
+                run_item<B, NDY, 1, PITCH, 1, K64, RB>(a, active, j, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
+                                                       s_key, tile_interior, dyi_lo, dyi_hi, X0, lane, ubase, dbase, slab_w);
             }
         }
     }
@@ -781,9 +776,9 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
         constexpr int per_warp = 32 / kFinLanes;
         const int grp = lane / kFinLanes;
         for (int jt = warp * per_warp + grp; jt < nblk * nrows; jt += nwarps * per_warp) {
-            const int jr = jt / nblk, jb = jt - jr * nblk;             // block row in the tile, block in the row
+            const int jr = MR ? jt / nblk : 0, jb = jt - jr * nblk;    // block row in the tile, block in the row
             const KeyT key = s_key[jr * a.tmb * G::NSUB + jb];
-            finalize_block<B>(a, pair, prevf, curf, tx * a.tmb * G::NSUB + jb, ty * a.tmr + jr, (uint32_t)(key >> RB),
+            finalize_block<B>(a, pair, prevf, curf, tx * a.tmb * G::NSUB + jb, ty * tmr + jr, (uint32_t)(key >> RB),
                               (uint32_t)(key & rmask), lane % kFinLanes, ((1u << kFinLanes) - 1u) << (grp * kFinLanes));
         }
     }
