@@ -72,6 +72,26 @@ def test_static_scratch_with_candidate_slabs(me):
             assert out.cpu().numpy().view(me.PAIR_DTYPE).tobytes() == est.fetch_pairs(len(pairs)).tobytes()
 
 
+def test_static_scratch_with_multi_row_tiles(me):
+    """A small range on a large frame is planned with tiles of several block rows; same records as the context path."""
+    import torch
+    from motion_estimation_b200 import synth
+    H, W = 720, 1280
+    cfg = me.SearchConfig(block=16, range=8)
+    stream = torch.cuda.current_stream().cuda_stream
+    frames, _ = synth.translating_frames(3, H, W, 7)
+    t = torch.from_numpy(frames).cuda().contiguous()
+    pairs = [(0, 1), (1, 2), (2, 0), (1, 0)]
+    with me.MotionEstimator(H, W, cfg, max_frames=3, max_pairs=4) as est:
+        assert est.geometry["tile_blocks_y"] > 1
+        for _ in range(2):
+            out = torch.zeros(len(pairs) * 6, dtype=torch.int32, device="cuda")
+            assert _static_search(me, t, pairs, cfg, out, stream) == 0, me._lib.lib().me_last_error()
+            torch.cuda.synchronize()
+            est.search_device(t.data_ptr(), t.stride(1), t.shape[0], pairs, stream=stream)
+            assert out.cpu().numpy().view(me.PAIR_DTYPE).tobytes() == est.fetch_pairs(len(pairs)).tobytes()
+
+
 def test_static_scratch_rejects_oversized_requests(me):
     import torch
     L = me._lib.lib()
