@@ -98,8 +98,8 @@ KernelChoice choice()
     k.fn_multirow = (const void *)&me::sad_search_kernel<B, kNDY, kNQ, PITCH, K64, RB, kMaxThreads, 3, true>;
     if constexpr (!K64) {
         constexpr int CW = B <= 16 ? me::kConsumerWarps : me::kConsumerWarps32;
-        k.fn_persistent = (const void *)&me::sad_search_persistent<B, kNDY, kNQ, PITCH, K64, RB, CW>;
-        k.persist_threads = 32 * (1 + CW);
+        k.fn_persistent = (const void *)&me::sad_search_persistent<B, kNDY, kNQ, PITCH, K64, RB, CW, me::kProducerWarps>;
+        k.persist_threads = 32 * (me::kProducerWarps + CW);
     }
     k.ndy = kNDY; k.nq = kNQ; k.maxt = kMaxThreads; k.pitch = PITCH; k.rank_bits = RB;
     return k;
@@ -275,6 +275,7 @@ int configure(me_ctx *c)
                     else if (!p.under) better = p.smem < best.smem;
                     else if ((p.nsx * p.nsy == 1) != (best.nsx * best.nsy == 1)) better = p.nsx * p.nsy == 1;   // no slabs when one window fits
                     else if (pw != bw) better = pw > bw;
+                    else if (pw == work_enough && p.tmr != best.tmr) better = p.tmr < best.tmr;   // enough work per row: keep one-row tiles (resident kernel)
                     else if (p.balance > best.balance + 0.015 || p.balance < best.balance - 0.015) better = p.balance > best.balance;
                     else if (p.nsx * p.nsy != best.nsx * best.nsy) better = p.nsx * p.nsy < best.nsx * best.nsy;
                     else if (p.tmb != best.tmb) better = p.tmb > best.tmb;
@@ -341,12 +342,14 @@ int configure(me_ctx *c)
     c->smem_persistent = me::kStages * c->pstage_bytes + (2 * me::kSelBins + 64) * 4 + 1024;
     if (c->smem_persistent > 227 * 1024 || !c->kc.fn_persistent || env_int("ME_PERSISTENT", 1) == 0) c->smem_persistent = 0;
     if (c->smem_persistent && env_int("ME_PERSISTENT", 1) != 2) {
-        // The resident kernel has ONE producer warp per SM: it only pays when searching a unit takes the
-        // consumer warps clearly longer than loading and shifting its window takes the producer
-        // (r01: +2 % at 1080p/16/+-32, but -40 % at +-8 and -5 % on slabbed searches).
+        // The resident kernel pays when searching a unit takes the consumer warps clearly longer than loading and
+        // shifting its window takes the producers.  Measured (r01f, tools/cmp_persist.sh): single-slab plans with
+        // a 16-byte aligned window origin win from a ratio of about 1.8 (8x8 +-48: +8 %, +-32: +3.5 %; 16x16 +-32:
+        // +2.5 %, 720p +-48: +4.6 %; 32x32 +-32: +1..2 %); slabbed searches lose 3-8 %, and windows that need the
+        // realigning copy build (R not a multiple of 16) lose or gain nothing (8x8 +-40: -2.6 %, 32x32 +-24: -2 %).
         const double t_cons = (double)a.tmb * NSUB * U * U * B * B / 256.0;                               // cycles at 64 lanes x 4 px
-        const double t_prod = 6000.0 + (double)a.n_row_boxes * a.box_rows * (c->win_pitch / 16) / 32.0 * 120.0;
-        if (a.nsx * a.nsy > 1 || t_cons < 2.7 * t_prod) c->smem_persistent = 0;
+        const double t_prod = 6000.0 + (double)a.n_row_boxes * a.box_rows * (c->win_pitch / 16) / 32.0 * 120.0 / me::kProducerWarps;
+        if (a.nsx * a.nsy > 1 || a.x_off != 0 || t_cons < 1.7 * t_prod) c->smem_persistent = 0;
     }
     if (a.tmr > 1) c->smem_persistent = 0;          // the resident kernel takes one block row per unit
 

@@ -26,7 +26,11 @@ namespace me {
 constexpr int kStages = 2;
 constexpr int kConsumerWarps = 20;        // 8/16-pixel blocks (80 registers per thread)
 constexpr int kConsumerWarps32 = 16;      // 32-pixel blocks: the patch needs ~110 registers
-constexpr int kPersistThreads = 32 * (1 + kConsumerWarps);
+#ifndef ME_NP
+#define ME_NP 2
+#endif
+constexpr int kProducerWarps = ME_NP;      // warps that build the shifted copies of a stage
+constexpr int kPersistThreads = 32 * (kProducerWarps + kConsumerWarps);
 
 struct UnitInfo {                  // one per stage: written by the producer, read by the consumers
     int pair, tile_id, tx, ty, prev_slot, cur_slot;
@@ -184,8 +188,8 @@ __device__ __forceinline__ void close_unit(const SearchArgs &a, const PersistArg
     }
 }
 
-template <int B, int NDY, int NQ, int PITCH, bool K64, int RB, int CW>
-__global__ void __launch_bounds__(32 * (1 + CW), 1)
+template <int B, int NDY, int NQ, int PITCH, bool K64, int RB, int CW, int NP>
+__global__ void __launch_bounds__(32 * (NP + CW), 1)
 sad_search_persistent(const __grid_constant__ CUtensorMap tm_win, const __grid_constant__ CUtensorMap tm_ref,
                       const SearchArgs a, const PersistArgs pa)
 {
@@ -210,7 +214,7 @@ sad_search_persistent(const __grid_constant__ CUtensorMap tm_win, const __grid_c
     if (tid == 0) {
         for (int s = 0; s < kStages; ++s) {
             mbar_init_only(&bars[s], 1);                       // full: one arrive.expect_tx + the TMA bytes
-            mbar_init_only(&bars[2 + s], 1);                   // ready: the producer
+            mbar_init_only(&bars[2 + s], NP);                  // ready: every producer warp
             mbar_init_only(&bars[4 + s], CW);                  // empty: every consumer warp
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -218,8 +222,9 @@ sad_search_persistent(const __grid_constant__ CUtensorMap tm_win, const __grid_c
     __syncthreads();
 
     const int stride = gridDim.x;
-    if (warp == 0) {
-        // ================================================================ producer
+    if (warp < NP) {
+        // ================================================================ producers: warp 0 issues the TMA boxes and
+        // writes the unit's control words, all NP warps build the shifted copies (chunk i goes to warp i mod NP)
         unsigned full_phase[kStages] = {0, 0};     // the TMA barrier only advances on units that load something
         for (int k = 0;; ++k) {
             const int u = blockIdx.x + k * stride;
@@ -231,11 +236,13 @@ sad_search_persistent(const __grid_constant__ CUtensorMap tm_win, const __grid_c
             uint8_t *s_raw = a.x_off ? s_win + 4 * (size_t)a.copy_bytes + 128 : s_win;
             uint8_t *s_ref = s_win + (size_t)a.n_bufs * a.copy_bytes + 128 + 256;
             KeyT *skeys = keys + s * kMaxKeys;
-            if (lane == 0) { info[s] = ui; claim[2 * s] = 0; claim[2 * s + 1] = 0; }
-            if (lane < kMaxKeys) skeys[lane] = kNone;
+            if (warp == 0) {
+                if (lane == 0) { info[s] = ui; claim[2 * s] = 0; claim[2 * s + 1] = 0; }
+                if (lane < kMaxKeys) skeys[lane] = kNone;
+            }
             if (ui.nd > 0) {
                 const int wx0 = ui.X0 - a.R - a.x_off + ui.ubase, wy0 = ui.Y0 - a.R + ui.dbase;
-                if (lane == 0) {
+                if (warp == 0 && lane == 0) {
                     const uint32_t bytes = (uint32_t)a.n_row_boxes * a.box_rows * PITCH + (uint32_t)ref_bytes;
                     mbar_expect_tx(&bars[s], bytes);
                     for (int rb = 0; rb < a.n_row_boxes; ++rb)
@@ -249,7 +256,7 @@ sad_search_persistent(const __grid_constant__ CUtensorMap tm_win, const __grid_c
                 const int chunks = a.n_row_boxes * a.box_rows * (PITCH >> 4);
                 const uint32_t *raw = reinterpret_cast<const uint32_t *>(s_raw);
                 if (a.x_off == 0) {
-                    for (int i = lane; i < chunks; i += 32) {
+                    for (int i = warp * 32 + lane; i < chunks; i += 32 * NP) {
                         const uint4 v = *reinterpret_cast<const uint4 *>(raw + 4 * i);
                         const uint32_t w4 = raw[4 * i + 4];
 #pragma unroll
@@ -263,7 +270,7 @@ sad_search_persistent(const __grid_constant__ CUtensorMap tm_win, const __grid_c
                         }
                     }
                 } else {
-                    for (int i = lane; i < chunks; i += 32) {
+                    for (int i = warp * 32 + lane; i < chunks; i += 32 * NP) {
                         uint32_t w[9];
                         const uint4 v0 = *reinterpret_cast<const uint4 *>(raw + 4 * i);
                         const uint4 v1 = *reinterpret_cast<const uint4 *>(raw + 4 * i + 4);
@@ -289,8 +296,8 @@ sad_search_persistent(const __grid_constant__ CUtensorMap tm_win, const __grid_c
             }
             __threadfence_block();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&bars[2 + s]);                      // unit published
-            if (ui.chunks_w + ui.chunks_n == 0)                            // no candidates here: the producer closes the unit itself
+            if (lane == 0) mbar_arrive(&bars[2 + s]);                      // this warp's share of the unit is published
+            if (warp == 0 && ui.chunks_w + ui.chunks_n == 0)               // no candidates here: the producer closes the unit itself
                 close_unit<B, K64, RB>(a, pa, ui, skeys, lane, nullptr);
         }
     } else {
