@@ -231,6 +231,8 @@ int configure(me_ctx *c)
             for (int tmr = 1; tmr <= (nsx * nsy == 1 ? 8 : 1); ++tmr) {
             if (forced_tmr && tmr != forced_tmr) continue;
             if (tmr > 1 && (tmr > a.nby || tmr * B > 256)) break;
+            // a row that already carries enough work stays a tile of its own (and can run in the resident kernel)
+            if (tmr > 1 && !forced_tmr && (long long)((kPitches[2] - a.x_off - (wmax - 1)) / MB) * NSUB * wmax * hmax >= work_enough) break;
             const int win_rows = ceil_div(hmax, NDY) * NDY + tmr * B - 1;
             const int n_row_boxes = ceil_div(win_rows, 256), box_rows = ceil_div(win_rows, n_row_boxes);
             const int alloc_rows = n_row_boxes * box_rows;
@@ -275,7 +277,6 @@ int configure(me_ctx *c)
                     else if (!p.under) better = p.smem < best.smem;
                     else if ((p.nsx * p.nsy == 1) != (best.nsx * best.nsy == 1)) better = p.nsx * p.nsy == 1;   // no slabs when one window fits
                     else if (pw != bw) better = pw > bw;
-                    else if (pw == work_enough && p.tmr != best.tmr) better = p.tmr < best.tmr;   // enough work per row: keep one-row tiles (resident kernel)
                     else if (p.balance > best.balance + 0.015 || p.balance < best.balance - 0.015) better = p.balance > best.balance;
                     else if (p.nsx * p.nsy != best.nsx * best.nsy) better = p.nsx * p.nsy < best.nsx * best.nsy;
                     else if (p.tmb != best.tmb) better = p.tmb > best.tmb;

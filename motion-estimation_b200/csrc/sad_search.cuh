@@ -205,15 +205,22 @@ __device__ __forceinline__ void sad_rows(const uint32_t *__restrict__ cur, const
 // 16x16 patch: the fully unrolled 36-row form is 80 KB of straight-line code and starved the warps of
 // instructions (r01e ncu: 1.9 no-instruction stalls per issue, still 1.0 with two 16-row halves); the price
 // is 4 extra window rows of loads per slice.
-template <int B, int NDY, int NQP, int PITCH, int LW>
+template <int B, int NDY, int NQP, int PITCH, int LW, bool SLICE16 = false>
 __device__ __forceinline__ void sad_patch(const uint32_t *__restrict__ cur, const uint32_t *__restrict__ ref,
                                           uint32_t (&acc)[Geo<B>::NSUB][NDY][NQP])
 {
-    if constexpr (B == 32) {
+    if constexpr (B == 16 && SLICE16) {
+        // multi-row tiles only (small ranges, short CTA phases): there the warps of an SM are spread over the whole
+        // kernel and the 20 KB unrolled body misses the instruction cache (ncu: 2.7 no-instruction stalls per issue at
+        // +-8); two rolled 8-row slices gave +13 % at +-8, +2.4 % at +-16.  4-row slices gained nothing more.
+#pragma unroll 1
+        for (int part = 0; part < 2; ++part)
+            sad_rows<B, 8, NDY, NQP, PITCH, LW>(cur + part * 8 * (PITCH / 4), ref + part * 8 * (kRefPitch / 4), acc);
+    } else if constexpr (B == 32) {
 #pragma unroll 1
         for (int part = 0; part < 4; ++part)
             sad_rows<B, 8, NDY, NQP, PITCH, LW>(cur + part * 8 * (PITCH / 4), ref + part * 8 * (kRefPitch / 4), acc);
-    } else {                                        // 16 rows as two slices measured slower (0.854 vs 0.867): the extra loads cost more
+    } else {                                        // one-row tiles: 16 rows as two slices measured slower (0.854 vs 0.867)
         sad_rows<B, B, NDY, NQP, PITCH, LW>(cur, ref, acc);
     }
 }
@@ -448,7 +455,7 @@ __device__ void reduce_pair(const SearchArgs &a, int pair, unsigned *scratch)
 
 // ---------------------------------------------------------------- one work item -> block keys
 // Runs one NDY x NQP candidate patch of macro-block j and folds its best candidate(s) into s_key.
-template <int B, int NDY, int NQP, int PITCH, int LW, bool K64, int RB>
+template <int B, int NDY, int NQP, int PITCH, int LW, bool K64, int RB, bool SLICE16 = false>
 __device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j, int dyg, int s, int q0,
                                          const uint8_t *s_win, const uint8_t *s_ref,
                                          typename KeyOf<K64>::T *s_key, bool tile_interior, int dyi_lo, int dyi_hi,
@@ -476,7 +483,7 @@ __device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j
         const uint32_t *cur = reinterpret_cast<const uint32_t *>(s_win + (size_t)s * (a.copy_bytes + kCopySkew)) +
                               (dyg * NDY + jy * B) * (PITCH / 4) + j * G::BW + q0;
         const uint32_t *ref = reinterpret_cast<const uint32_t *>(s_ref) + jy * B * (kRefPitch / 4) + j * G::BW;
-        sad_patch<B, NDY, NQP, PITCH, LW>(cur, ref, acc);
+        sad_patch<B, NDY, NQP, PITCH, LW, SLICE16>(cur, ref, acc);
 
         // everything below is in SLAB-LOCAL index space: u = dx + R - ubase, dyi = dy + R - dbase
         const int dyi0 = dyg * NDY, u0 = 4 * q0 + s;
@@ -546,6 +553,7 @@ __device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j
 // ---------------------------------------------------------------- the search kernel
 // MR = tiles of several block rows (a.tmr > 1).  A separate instantiation: carrying the row arithmetic in the
 // one-row kernel cost it 3 % (r01e: 0.846 -> 0.819 at 1080p/16/+-32).
+constexpr bool kSliceMR = true;               // multi-row tiles (small ranges): 16-row patches as two rolled 8-row slices
 template <int B, int NDY, int NQ, int PITCH, bool K64, int RB, int MAXT, int MINB, bool MR>
 __global__ void __launch_bounds__(MAXT, MINB)
 sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_constant__ CUtensorMap tm_ref,
@@ -710,7 +718,7 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
             if constexpr (MR) {
                 int jx, jy, lo, hi; bool inter;
                 row_domain(j, dyg, active, jx, jy, lo, hi, inter);
-                run_item<B, NDY, NQ, PITCH, LWW, K64, RB>(a, active, jx, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
+                run_item<B, NDY, NQ, PITCH, LWW, K64, RB, kSliceMR>(a, active, jx, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
                                                           s_key, inter, lo, hi, X0, lane, ubase, dbase, slab_w, jy, jy * key_stride);
             } else {
                 run_item<B, NDY, NQ, PITCH, LWW, K64, RB>(a, active, j, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
@@ -734,7 +742,7 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
             if constexpr (MR) {
                 int jx, jy, lo, hi; bool inter;
                 row_domain(j, dyg, active, jx, jy, lo, hi, inter);
-                run_item<B, NDY, 1, PITCH, 1, K64, RB>(a, active, jx, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
+                run_item<B, NDY, 1, PITCH, 1, K64, RB, kSliceMR>(a, active, jx, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
                                                        s_key, inter, lo, hi, X0, lane, ubase, dbase, slab_w, jy, jy * key_stride);
             } else {
                 run_item<B, NDY, 1, PITCH, 1, K64, RB>(a, active, j, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
