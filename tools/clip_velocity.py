@@ -18,7 +18,12 @@ for name, rng in (("29.1", 32), ("58.2", 32), ("116.4", 64)):
     lines = open(ingest.find_timestamps(d)).read().split("\n")
     n = min(len(frames), sum(1 for l in lines[1:] if l.strip()) - 1)
     frames = frames[:n]
-    for units in ("reference", "fullres"):
+    if len(sys.argv) > 1 and sys.argv[1] == "preprocess":          # the reference's default pipeline: CLAHE, then non-local means
+        t0 = time.time(); frames = api.adaptive_histogram_equalization(frames); t_eq = time.time() - t0
+        t0 = time.time(); frames = api.denoise_hf5(frames, n_list=len(frames) + 1); t_nlm = time.time() - t0
+        print(f"{name}: CLAHE of {len(frames)} frames {t_eq:.2f}s, NLM (h=15, 19/41, 1/5/9 frames) {t_nlm:.2f}s "
+              f"= {t_nlm / len(frames) * 1e3:.2f} ms/frame incl. host copies", flush=True)
+    for units in (("fullres",) if len(sys.argv) > 1 else ("reference", "fullres")):
         t0 = time.time()
         res = api.end_process(frames, imagePath=d, firstFrame=0, config=me.SearchConfig(block=16, range=rng),
                               units=units, return_details=True)
