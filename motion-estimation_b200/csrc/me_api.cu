@@ -343,14 +343,17 @@ int configure(me_ctx *c)
     c->smem_persistent = me::kStages * c->pstage_bytes + (2 * me::kSelBins + 64) * 4 + 1024;
     if (c->smem_persistent > 227 * 1024 || !c->kc.fn_persistent || env_int("ME_PERSISTENT", 1) == 0) c->smem_persistent = 0;
     if (c->smem_persistent && env_int("ME_PERSISTENT", 1) != 2) {
-        // The resident kernel pays when searching a unit takes the consumer warps clearly longer than loading and
-        // shifting its window takes the producers.  Measured (r01f, tools/cmp_persist.sh): single-slab plans with
-        // a 16-byte aligned window origin win from a ratio of about 1.8 (8x8 +-48: +8 %, +-32: +3.5 %; 16x16 +-32:
-        // +2.5 %, 720p +-48: +4.6 %; 32x32 +-32: +1..2 %); slabbed searches lose 3-8 %, and windows that need the
-        // realigning copy build (R not a multiple of 16) lose or gain nothing (8x8 +-40: -2.6 %, 32x32 +-24: -2 %).
-        const double t_cons = (double)a.tmb * NSUB * U * U * B * B / 256.0;                               // cycles at 64 lanes x 4 px
-        const double t_prod = 6000.0 + (double)a.n_row_boxes * a.box_rows * (c->win_pitch / 16) / 32.0 * 120.0 / me::kProducerWarps;
-        if (a.nsx * a.nsy > 1 || a.x_off != 0 || t_cons < 1.7 * t_prod) c->smem_persistent = 0;
+        // The resident kernel pays when searching a unit (tile x slab) takes the consumer warps clearly longer than
+        // loading and shifting its window takes the producers; the realigning copy build of windows whose origin is
+        // not 16-byte aligned (R not a multiple of 16) costs about three times the plain one.  Measured (r01f,
+        // tools/cmp_persist.sh, one-row tiles): wins from a ratio of about 1.7 -- 16x16 +-32 +2.5 %, +-48 +4.6 %,
+        // +-64 (2x3 slabs) +2.3 %, 4K +-64 +4.5 %; 8x8 +-32 +2.5 %, +-48 +8 %, 4K +-64 (1x2 slabs) +9 %; 32x32 +-32
+        // +2 %, +-40 +12 % -- and loses below it (8x8 +-24: -13 %, 16x16 +-20: -2 %).
+        const double cand = (double)U * U / (a.nsx * a.nsy);                                             // candidates of an average slab
+        const double t_cons = (double)a.tmb * NSUB * cand * B * B / 256.0;                               // cycles at 64 lanes x 4 px
+        const double build = (double)a.n_row_boxes * a.box_rows * (c->win_pitch / 16) / 32.0 * 120.0 / me::kProducerWarps;
+        const double t_prod = 6000.0 + build * (a.x_off ? 3.0 : 1.0);
+        if (t_cons < 1.7 * t_prod) c->smem_persistent = 0;
     }
     if (a.tmr > 1) c->smem_persistent = 0;          // the resident kernel takes one block row per unit
 
@@ -407,7 +410,7 @@ int launch_search(me_ctx *c, const uint8_t *frames, const CUtensorMap &tm_win, c
         me::PersistArgs pa;
         pa.n_units = (int)units; pa.n_pairs = n_pairs; pa.stage_bytes = c->pstage_bytes;
         pa.ready_pairs = c->d_ready; pa.error_flag = c->d_error;
-        CU_TRY(cudaMemsetAsync(c->d_ready, 0xff, sizeof(int) * (size_t)(n_pairs + 1), st));
+        CU_TRY(cudaMemsetAsync(c->d_ready, 0xff, sizeof(int) * (size_t)(n_pairs + 2), st));   // pair queue + unit counter
         void *params[4] = {(void *)&tm_win, (void *)&tm_ref, (void *)&a, (void *)&pa};
         const unsigned grid = units < c->sm_count ? (unsigned)units : (unsigned)c->sm_count;
         CU_TRY(cudaLaunchKernel(c->kc.fn_persistent, dim3(grid), dim3((unsigned)c->kc.persist_threads), params,
@@ -617,7 +620,7 @@ int me_create(int device, int height, int width, const me_params *params, int ma
         CREATE_TRY(cudaMalloc(&c->args.tile_ticket, nt * sizeof(unsigned)));
         CREATE_TRY(cudaMemset(c->args.tile_ticket, 0, nt * sizeof(unsigned)));
     }
-    CREATE_TRY(cudaMalloc(&c->d_ready, sizeof(int) * (size_t)(max_pairs + 1)));
+    CREATE_TRY(cudaMalloc(&c->d_ready, sizeof(int) * (size_t)(max_pairs + 2)));
     CREATE_TRY(cudaMalloc(&c->d_error, sizeof(int)));
     CREATE_TRY(cudaMemset(c->d_error, 0, sizeof(int)));
     if (c->smem_persistent) {

@@ -46,7 +46,8 @@ struct PersistArgs {
     int n_units;                   // tiles_per_pair * nslab * n_pairs
     int n_pairs;
     int stage_bytes;               // window copies (+raw) + slack + reference strip, multiple of 128
-    int *ready_pairs;              // [n_pairs + 1]: [0] = counter (starts at -1), then pair ids (-1 = not yet)
+    int *ready_pairs;              // [n_pairs + 2]: [0] = counter (starts at -1), then pair ids (-1 = not yet),
+                                   // [n_pairs + 1] = the launch's unit counter (starts at -1)
     int *error_flag;               // set when a wait timed out (never in a correct run)
 };
 
@@ -221,16 +222,35 @@ sad_search_persistent(const __grid_constant__ CUtensorMap tm_win, const __grid_c
     }
     __syncthreads();
 
+    // Units are handed out through one global counter (not a fixed stride per CTA): slabs of different size, border
+    // tiles and skipped slabs make unit costs uneven, and a static split left SMs idle at the end of slabbed launches
+    // (r01f ncu: ALU pipe 95 % busy while active, yet 3 % slower than one CTA per tile).
     const int stride = gridDim.x;
+    int *unit_counter = pa.ready_pairs + pa.n_pairs + 1;
+    int *s_unit = reinterpret_cast<int *>(bars + 6) + 4;          // [kStages] unit of the stage, shared by the producer warps
     if (warp < NP) {
         // ================================================================ producers: warp 0 issues the TMA boxes and
         // writes the unit's control words, all NP warps build the shifted copies (chunk i goes to warp i mod NP)
         unsigned full_phase[kStages] = {0, 0};     // the TMA barrier only advances on units that load something
         for (int k = 0;; ++k) {
-            const int u = blockIdx.x + k * stride;
-            if (u >= pa.n_units) break;
             const int s = k & 1, use = k >> 1;
             if (use > 0) mbar_wait_relaxed(&bars[4 + s], (use - 1) & 1);
+            int u = 0;
+            if (NP == 1) {
+                if (lane == 0) u = atomicAdd(unit_counter, 1) + 1;
+                u = __shfl_sync(kFull, u, 0);
+            } else {
+                if (warp == 0 && lane == 0) s_unit[s] = atomicAdd(unit_counter, 1) + 1;
+                asm volatile("bar.sync 1, %0;" ::"n"(32 * NP) : "memory");      // producer warps only
+                u = s_unit[s];
+            }
+            if (u >= pa.n_units) {                                         // nothing left: tell the consumers and leave
+                if (warp == 0 && lane == 0) info[s].pair = -1;
+                __threadfence_block();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&bars[2 + s]);
+                break;
+            }
             const UnitInfo ui = decode_unit<B, NDY>(a, u);
             uint8_t *s_win = smem + (size_t)s * pa.stage_bytes;      // address arithmetic on the __shared__ symbol keeps LDS/STS
             uint8_t *s_raw = a.x_off ? s_win + 4 * (size_t)a.copy_bytes + 128 : s_win;
@@ -303,11 +323,10 @@ sad_search_persistent(const __grid_constant__ CUtensorMap tm_win, const __grid_c
     } else {
         // ================================================================ consumers
         for (int k = 0;; ++k) {
-            const int u = blockIdx.x + k * stride;
-            if (u >= pa.n_units) break;
             const int s = k & 1, use = k >> 1;
             mbar_wait(&bars[2 + s], use & 1);
             const UnitInfo &ui = info[s];
+            if (ui.pair < 0) break;                                        // the producer found the unit counter exhausted
             const uint8_t *s_win = smem + (size_t)s * pa.stage_bytes;
             const uint8_t *s_ref = s_win + (size_t)a.n_bufs * a.copy_bytes + 128 + 256;
             KeyT *skeys = keys + s * kMaxKeys;
