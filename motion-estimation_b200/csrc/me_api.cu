@@ -96,8 +96,8 @@ KernelChoice choice()
     KernelChoice k;
     k.fn = (const void *)&me::sad_search_kernel<B, kNDY, kNQ, PITCH, K64, RB, kMaxThreads, 3, false>;
     k.fn_multirow = (const void *)&me::sad_search_kernel<B, kNDY, kNQ, PITCH, K64, RB, kMaxThreads, 3, true>;
-    if constexpr (!K64) {
-        constexpr int CW = B <= 16 ? me::kConsumerWarps : me::kConsumerWarps32;
+    {
+        constexpr int CW = (B <= 16 && !K64) ? me::kConsumerWarps : me::kConsumerWarps32;
         k.fn_persistent = (const void *)&me::sad_search_persistent<B, kNDY, kNQ, PITCH, K64, RB, CW, me::kProducerWarps>;
         k.persist_threads = 32 * (me::kProducerWarps + CW);
     }
