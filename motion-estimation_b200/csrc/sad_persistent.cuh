@@ -124,9 +124,12 @@ __device__ __forceinline__ UnitInfo decode_unit(const SearchArgs &a, int u)
 // `keys` = the stage's block minima in shared memory.  Returns after the stage may be reused by this warp.
 // `release` (may be null): the stage's "empty" barrier; it is signalled as soon as the keys are in registers,
 // long before the global-memory part of the finalize step is over.
-template <int B, bool K64, int RB>
+// `s_win` / `s_ref` (may be null): the stage's window copies and reference strip.  A single-slab unit finalizes from
+// them (finalize_block_smem) and releases the stage after that short loop instead of before the global-memory one.
+template <int B, int PITCH, bool K64, int RB>
 __device__ __forceinline__ void close_unit(const SearchArgs &a, const PersistArgs &pa, const UnitInfo &ui,
-                                           typename KeyOf<K64>::T *keys, int lane, uint64_t *release)
+                                           typename KeyOf<K64>::T *keys, int lane, uint64_t *release,
+                                           const uint8_t *s_win = nullptr, const uint8_t *s_ref = nullptr)
 {
     using KeyT = typename KeyOf<K64>::T;
     using G = Geo<B>;
@@ -136,7 +139,11 @@ __device__ __forceinline__ void close_unit(const SearchArgs &a, const PersistArg
 #pragma unroll
     for (int i = 0; i < (kMaxKeys + 31) / 32; ++i) mykey[i] = lane + 32 * i < ui.nblk ? keys[lane + 32 * i] : kNone;
     __syncwarp();
-    if (release && lane == 0) mbar_arrive(release);
+    // ... for 16- and 32-pixel blocks (r01f: 0.861 -> 0.870, 32x32 0.867 -> 0.888).  Units of 8x8 blocks hold 12-24
+    // blocks; keeping the stage through their finalize stalls the producer (+-32: 0.71 -> 0.64, +-48: 0.68 -> 0.65), so
+    // they release first and finalize from global memory as before.
+    const bool from_smem = B >= 16 && nslab == 1 && s_win != nullptr;
+    if (!from_smem && release && lane == 0) mbar_arrive(release);
     if (nslab > 1) {
         const size_t kbase = (size_t)ui.pair * a.nb + (size_t)ui.ty * a.nbx + (size_t)ui.tx * a.tmb * G::NSUB;
         KeyT *gkey = reinterpret_cast<KeyT *>(a.blk_key);
@@ -173,11 +180,18 @@ __device__ __forceinline__ void close_unit(const SearchArgs &a, const PersistArg
             const KeyT k = __shfl_sync(kFull, mykey[i], src);
             if ((jb >> 5) == i) key = k;
         }
-        if (jb < ui.nblk)
-            finalize_block<B>(a, ui.pair, prevf, curf, ui.tx * a.tmb * G::NSUB + jb, ui.ty, (uint32_t)(key >> RB),
-                              (uint32_t)(key & rmask), lane % kFinLanes, ((1u << kFinLanes) - 1u) << (grp * kFinLanes));
+        if (jb < ui.nblk) {
+            const unsigned fmask = ((1u << kFinLanes) - 1u) << (grp * kFinLanes);
+            if (from_smem)
+                finalize_block_smem<B, PITCH>(a, ui.pair, s_win, s_ref, 0, jb, ui.tx * a.tmb * G::NSUB + jb, ui.ty,
+                                              (uint32_t)(key >> RB), (uint32_t)(key & rmask), lane % kFinLanes, fmask);
+            else
+                finalize_block<B>(a, ui.pair, prevf, curf, ui.tx * a.tmb * G::NSUB + jb, ui.ty, (uint32_t)(key >> RB),
+                                  (uint32_t)(key & rmask), lane % kFinLanes, fmask);
+        }
     }
     __syncwarp();
+    if (from_smem && release && lane == 0) mbar_arrive(release);
     if (lane == 0) {
         __threadfence();
         const unsigned old = atomicAdd(&a.pair_ticket[ui.pair], 1u);
@@ -318,7 +332,7 @@ sad_search_persistent(const __grid_constant__ CUtensorMap tm_win, const __grid_c
             __syncwarp();
             if (lane == 0) mbar_arrive(&bars[2 + s]);                      // this warp's share of the unit is published
             if (warp == 0 && ui.chunks_w + ui.chunks_n == 0)               // no candidates here: the producer closes the unit itself
-                close_unit<B, K64, RB>(a, pa, ui, skeys, lane, nullptr);
+                close_unit<B, PITCH, K64, RB>(a, pa, ui, skeys, lane, nullptr);
         }
     } else {
         // ================================================================ consumers
@@ -367,7 +381,7 @@ sad_search_persistent(const __grid_constant__ CUtensorMap tm_win, const __grid_c
                 if (old == (unsigned)nchunks - 1u) {                       // this warp finished the unit's last chunk
                     __threadfence_block();
                     const UnitInfo mine = ui;                              // private copy: the stage is released inside close_unit
-                    close_unit<B, K64, RB>(a, pa, mine, skeys, lane, &bars[4 + s]);
+                    close_unit<B, PITCH, K64, RB>(a, pa, mine, skeys, lane, &bars[4 + s], s_win, s_ref);
                     released = true;
                     break;
                 }

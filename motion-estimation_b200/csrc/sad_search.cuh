@@ -255,39 +255,11 @@ __device__ __forceinline__ float funkey(uint32_t k)
     return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
 }
 
-// Eight lanes (one quarter of a warp, `mask` names them, `lane` = 0..7 inside the group): neighbour SADs,
-// gates, parabola, per-block record.  Four blocks are finalized per warp pass.
-constexpr int kFinLanes = 8;
-template <int B>
-__device__ __forceinline__ void finalize_block(const SearchArgs &a, int pair, const uint8_t *prevf,
-                                               const uint8_t *curf, int bx, int by, uint32_t sad, uint32_t rank,
-                                               int lane, unsigned mask)
+// Reduction over the block's kFinLanes lanes, gates, parabola, the 17-byte record (lane 0 writes).
+__device__ __forceinline__ void finalize_record(const SearchArgs &a, int pair, int bx, int by, uint32_t sad, int dx, int dy,
+                                                bool xin, bool yin, uint32_t sxm, uint32_t sxp, uint32_t sym, uint32_t syp,
+                                                uint32_t vmn, uint32_t vmx, int lane, unsigned mask)
 {
-    constexpr int SW = B / 4;
-    const int R = a.R, U = a.U, x0 = bx * B, y0 = by * B;
-    const int dyi = (int)(rank / (uint32_t)U), ui = (int)rank - dyi * U;
-    const int dx = ui - R, dy = dyi - R;
-    const int dxlo = max(-R, -x0), dxhi = min(R, a.W - B - x0);
-    const int dylo = max(-R, -y0), dyhi = min(R, a.H - B - y0);
-    const bool xin = dx - 1 >= dxlo && dx + 1 <= dxhi;
-    const bool yin = dy - 1 >= dylo && dy + 1 <= dyhi;
-    const size_t pitch = (size_t)a.frame_pitch;
-    uint32_t sxm = 0, sxp = 0, sym = 0, syp = 0, vmn = 0xffffffffu, vmx = 0u;
-    for (int idx = lane; idx < B * SW; idx += kFinLanes) {
-        const int row = idx / SW, wd = idx - row * SW;
-        const uint32_t rw = __ldg(reinterpret_cast<const uint32_t *>(prevf + (size_t)(y0 + row) * pitch + x0) + wd);
-        vmn = __vminu4(vmn, rw);
-        vmx = __vmaxu4(vmx, rw);
-        const uint8_t *c = curf + (size_t)(y0 + dy + row) * pitch + (x0 + dx + 4 * wd);
-        if (xin) {
-            sxm = vsad4(rw, ld_bytes4(c - 1), sxm);
-            sxp = vsad4(rw, ld_bytes4(c + 1), sxp);
-        }
-        if (yin) {
-            sym = vsad4(rw, ld_bytes4(c - pitch), sym);
-            syp = vsad4(rw, ld_bytes4(c + pitch), syp);
-        }
-    }
     sxm = __reduce_add_sync(mask, sxm);
     sxp = __reduce_add_sync(mask, sxp);
     sym = __reduce_add_sync(mask, sym);
@@ -321,6 +293,85 @@ __device__ __forceinline__ void finalize_block(const SearchArgs &a, int pair, co
         __threadfence();
     }
 }
+
+
+// Eight lanes (one quarter of a warp, `mask` names them, `lane` = 0..7 inside the group): neighbour SADs,
+// gates, parabola, per-block record.  Four blocks are finalized per warp pass.
+constexpr int kFinLanes = 8;
+template <int B>
+__device__ __forceinline__ void finalize_block(const SearchArgs &a, int pair, const uint8_t *prevf,
+                                               const uint8_t *curf, int bx, int by, uint32_t sad, uint32_t rank,
+                                               int lane, unsigned mask)
+{
+    constexpr int SW = B / 4;
+    const int R = a.R, U = a.U, x0 = bx * B, y0 = by * B;
+    const int dyi = (int)(rank / (uint32_t)U), ui = (int)rank - dyi * U;
+    const int dx = ui - R, dy = dyi - R;
+    const int dxlo = max(-R, -x0), dxhi = min(R, a.W - B - x0);
+    const int dylo = max(-R, -y0), dyhi = min(R, a.H - B - y0);
+    const bool xin = dx - 1 >= dxlo && dx + 1 <= dxhi;
+    const bool yin = dy - 1 >= dylo && dy + 1 <= dyhi;
+    const size_t pitch = (size_t)a.frame_pitch;
+    uint32_t sxm = 0, sxp = 0, sym = 0, syp = 0, vmn = 0xffffffffu, vmx = 0u;
+    for (int idx = lane; idx < B * SW; idx += kFinLanes) {
+        const int row = idx / SW, wd = idx - row * SW;
+        const uint32_t rw = __ldg(reinterpret_cast<const uint32_t *>(prevf + (size_t)(y0 + row) * pitch + x0) + wd);
+        vmn = __vminu4(vmn, rw);
+        vmx = __vmaxu4(vmx, rw);
+        const uint8_t *c = curf + (size_t)(y0 + dy + row) * pitch + (x0 + dx + 4 * wd);
+        if (xin) {
+            sxm = vsad4(rw, ld_bytes4(c - 1), sxm);
+            sxp = vsad4(rw, ld_bytes4(c + 1), sxp);
+        }
+        if (yin) {
+            sym = vsad4(rw, ld_bytes4(c - pitch), sym);
+            syp = vsad4(rw, ld_bytes4(c + pitch), syp);
+        }
+    }
+    finalize_record(a, pair, bx, by, sad, dx, dy, xin, yin, sxm, sxp, sym, syp, vmn, vmx, lane, mask);
+}
+
+// Same step for a CTA that still holds the block's whole candidate window in shared memory (single-slab tiles):
+// the neighbour SADs come from the shifted copies with aligned word loads -- no global loads, no realignment,
+// no 64-bit address arithmetic (r01f ncu at +-8: the global-memory form was ~15 % of all issued instructions
+// and the source of the long-scoreboard stalls).  jr / jb: block row in the tile / block in the row.
+template <int B, int PITCH>
+__device__ __forceinline__ void finalize_block_smem(const SearchArgs &a, int pair, const uint8_t *s_win, const uint8_t *s_ref,
+                                                    int jr, int jb, int bx, int by, uint32_t sad, uint32_t rank,
+                                                    int lane, unsigned mask)
+{
+    constexpr int SW = B / 4, PW = PITCH / 4, RPW = kRefPitch / 4;
+    const int R = a.R, U = a.U, x0 = bx * B, y0 = by * B;
+    const int dyi = (int)(rank / (uint32_t)U), ui = (int)rank - dyi * U;
+    const int dx = ui - R, dy = dyi - R;
+    const int dxlo = max(-R, -x0), dxhi = min(R, a.W - B - x0);
+    const int dylo = max(-R, -y0), dyhi = min(R, a.H - B - y0);
+    const bool xin = dx - 1 >= dxlo && dx + 1 <= dxhi;
+    const bool yin = dy - 1 >= dylo && dy + 1 <= dyhi;
+    const size_t cstride = (size_t)a.copy_bytes + kCopySkew;
+    // word pointers of the candidate (u, dyi) = copy u & 3, row dyi + jr*B, word jb*SW + (u >> 2)
+    auto cand = [&](int u, int d) {
+        return reinterpret_cast<const uint32_t *>(s_win + (size_t)(u & 3) * cstride) + (d + jr * B) * PW + jb * SW + (u >> 2);
+    };
+    const uint32_t *ref = reinterpret_cast<const uint32_t *>(s_ref) + jr * B * RPW + jb * SW;
+    const uint32_t *cxm = cand(xin ? ui - 1 : ui, dyi), *cxp = cand(xin ? ui + 1 : ui, dyi);
+    const uint32_t *cym = cand(ui, yin ? dyi - 1 : dyi), *cyp = cand(ui, yin ? dyi + 1 : dyi);
+    uint32_t sxm = 0, sxp = 0, sym = 0, syp = 0, vmn = 0xffffffffu, vmx = 0u;
+#pragma unroll 2
+    for (int idx = lane; idx < B * SW; idx += kFinLanes) {
+        const int row = idx / SW, wd = idx - row * SW;
+        const uint32_t rw = ref[row * RPW + wd];
+        vmn = __vminu4(vmn, rw);
+        vmx = __vmaxu4(vmx, rw);
+        const int o = row * PW + wd;
+        sxm = vsad4(rw, cxm[o], sxm);
+        sxp = vsad4(rw, cxp[o], sxp);
+        sym = vsad4(rw, cym[o], sym);
+        syp = vsad4(rw, cyp[o], syp);
+    }
+    finalize_record(a, pair, bx, by, sad, dx, dy, xin, yin, sxm, sxp, sym, syp, vmn, vmx, lane, mask);
+}
+
 
 // ---------------------------------------------------------------- per-pair median (last CTA)
 // The CTA that takes the pair's last ticket reduces it while the rest of the grid works on other
@@ -786,8 +837,13 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
         for (int jt = warp * per_warp + grp; jt < nblk * nrows; jt += nwarps * per_warp) {
             const int jr = MR ? jt / nblk : 0, jb = jt - jr * nblk;    // block row in the tile, block in the row
             const KeyT key = s_key[jr * a.tmb * G::NSUB + jb];
-            finalize_block<B>(a, pair, prevf, curf, tx * a.tmb * G::NSUB + jb, ty * tmr + jr, (uint32_t)(key >> RB),
-                              (uint32_t)(key & rmask), lane % kFinLanes, ((1u << kFinLanes) - 1u) << (grp * kFinLanes));
+            const unsigned fmask = ((1u << kFinLanes) - 1u) << (grp * kFinLanes);
+            if (nslab == 1)        // the whole candidate square of the block is still in this CTA's shared memory
+                finalize_block_smem<B, PITCH>(a, pair, s_win, s_ref, jr, jb, tx * a.tmb * G::NSUB + jb, ty * tmr + jr,
+                                              (uint32_t)(key >> RB), (uint32_t)(key & rmask), lane % kFinLanes, fmask);
+            else
+                finalize_block<B>(a, pair, prevf, curf, tx * a.tmb * G::NSUB + jb, ty * tmr + jr, (uint32_t)(key >> RB),
+                                  (uint32_t)(key & rmask), lane % kFinLanes, fmask);
         }
     }
     __syncthreads();
