@@ -507,7 +507,7 @@ __device__ void reduce_pair(const SearchArgs &a, int pair, unsigned *scratch)
 // ---------------------------------------------------------------- one work item -> block keys
 // Runs one NDY x NQP candidate patch of macro-block j and folds its best candidate(s) into s_key.
 template <int B, int NDY, int NQP, int PITCH, int LW, bool K64, int RB, bool SLICE16 = false>
-__device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j, int dyg, int s, int q0,
+__device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j, int dyi0, int s, int q0,
                                          const uint8_t *s_win, const uint8_t *s_ref,
                                          typename KeyOf<K64>::T *s_key, bool tile_interior, int dyi_lo, int dyi_hi,
                                          int X0, int lane, int ubase, int dbase, int slab_w, int jy = 0, int key_row = 0)
@@ -532,12 +532,12 @@ __device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j
 #pragma unroll
                 for (int q = 0; q < NQP; ++q) acc[sb][d][q] = 0;
         const uint32_t *cur = reinterpret_cast<const uint32_t *>(s_win + (size_t)s * (a.copy_bytes + kCopySkew)) +
-                              (dyg * NDY + jy * B) * (PITCH / 4) + j * G::BW + q0;
+                              (dyi0 + jy * B) * (PITCH / 4) + j * G::BW + q0;
         const uint32_t *ref = reinterpret_cast<const uint32_t *>(s_ref) + jy * B * (kRefPitch / 4) + j * G::BW;
         sad_patch<B, NDY, NQP, PITCH, LW, SLICE16>(cur, ref, acc);
 
         // everything below is in SLAB-LOCAL index space: u = dx + R - ubase, dyi = dy + R - dbase
-        const int dyi0 = dyg * NDY, u0 = 4 * q0 + s;
+        const int u0 = 4 * q0 + s;
         int u_lo[G::NSUB], u_hi[G::NSUB];
         bool whole = dyi0 >= dyi_lo && dyi0 + NDY - 1 <= dyi_hi;
 #pragma unroll
@@ -653,6 +653,10 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     const bool x_interior = a.R - X0 - ubase <= 0 && min(twoR, a.R + a.W - B - xlast) - ubase >= slab_w - 1;
     const bool tile_interior = x_interior && a.R - Y0 - dbase <= 0 && min(twoR, a.R + a.H - B - Ylast) - dbase >= slab_h - 1;
     const int dyg_lo = dyi_lo / NDY, dyg_hi = dyi_hi >= 0 ? dyi_hi / NDY : -1;
+    // The last dy group of a slab whose height is not a multiple of NDY starts NDY rows before the slab's end instead of
+    // hanging over it: its first rows repeat candidates of the group before (same keys, harmless for the argmin), and
+    // the group stays on the test-free argmin path instead of carrying masked rows (a quarter of all items at +-8).
+    const int dy_cap = max(0, slab_h - NDY);
     const int nd = dyi_hi >= dyi_lo ? dyg_hi - dyg_lo + 1 : 0;         // 0: this slab holds no candidate of this block row
     if (tid < kMaxTileKeys) s_key[tid] = kNone;
 
@@ -746,12 +750,12 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     const unsigned magic_row = a.magic_nj[tx == a.tiles_x - 1];
     const int key_stride = a.tmb;                                      // macro-block slots per row of s_key
     // row of macro-block jj, and that row's own share of the dy domain
-    auto row_domain = [&](int jj, int dyg, bool &act, int &jx, int &jy, int &lo, int &hi, bool &inter) {
+    auto row_domain = [&](int jj, int dyi0, bool &act, int &jx, int &jy, int &lo, int &hi, bool &inter) {
         jy = fastdiv(jj, magic_row); jx = jj - jy * nj;
         const int y0r = Y0 + jy * B;
         lo = max(0, a.R - y0r - dbase); hi = min(slab_h - 1, min(twoR, a.R + a.H - B - y0r) - dbase);
         inter = x_interior && lo == 0 && hi == slab_h - 1;
-        act = act && dyg * NDY + NDY - 1 >= lo && dyg * NDY <= hi;      // a dy group wholly outside this row's range: nothing to do
+        act = act && dyi0 + NDY - 1 >= lo && dyi0 <= hi;                // a dy group wholly outside this row's range: nothing to do
     };
     for (int rep = 0; rep < a.repeat; ++rep) {
     if (nd > 0) {   // wide patches: NDY x NQ
@@ -764,15 +768,16 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
             bool active = w_raw < total;
             const int w = active ? w_raw : total - 1;
             const int j = fastdiv(w, magic_pj), r = w - j * per_j;
-            const int dq = fastdiv(r, a.magic_nw[lastx]), cg = r - dq * n_wide, dyg = dyg_lo + dq;   // column group varies fastest across lanes
+            const int dq = fastdiv(r, a.magic_nw[lastx]), cg = r - dq * n_wide;                       // column group varies fastest across lanes
+            const int dyi0 = min((dyg_lo + dq) * NDY, dy_cap);
             const unsigned g = grp[cg];
             if constexpr (MR) {
                 int jx, jy, lo, hi; bool inter;
-                row_domain(j, dyg, active, jx, jy, lo, hi, inter);
-                run_item<B, NDY, NQ, PITCH, LWW, K64, RB, kSliceMR>(a, active, jx, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
+                row_domain(j, dyi0, active, jx, jy, lo, hi, inter);
+                run_item<B, NDY, NQ, PITCH, LWW, K64, RB, kSliceMR>(a, active, jx, dyi0, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
                                                           s_key, inter, lo, hi, X0, lane, ubase, dbase, slab_w, jy, jy * key_stride);
             } else {
-                run_item<B, NDY, NQ, PITCH, LWW, K64, RB>(a, active, j, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
+                run_item<B, NDY, NQ, PITCH, LWW, K64, RB>(a, active, j, dyi0, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
                                                           s_key, tile_interior, dyi_lo, dyi_hi, X0, lane, ubase, dbase, slab_w);
             }
         }
@@ -788,15 +793,16 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
             bool active = w_raw < total;
             const int w = active ? w_raw : total - 1;
             const int j = fastdiv(w, magic_pj), r = w - j * per_j;
-            const int dq = fastdiv(r, a.magic_nn[lastx]), cg = r - dq * n_narrow, dyg = dyg_lo + dq;
+            const int dq = fastdiv(r, a.magic_nn[lastx]), cg = r - dq * n_narrow;
+            const int dyi0 = min((dyg_lo + dq) * NDY, dy_cap);
             const unsigned g = grp[n_wide + cg];
             if constexpr (MR) {
                 int jx, jy, lo, hi; bool inter;
-                row_domain(j, dyg, active, jx, jy, lo, hi, inter);
-                run_item<B, NDY, 1, PITCH, 1, K64, RB, kSliceMR>(a, active, jx, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
+                row_domain(j, dyi0, active, jx, jy, lo, hi, inter);
+                run_item<B, NDY, 1, PITCH, 1, K64, RB, kSliceMR>(a, active, jx, dyi0, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
                                                        s_key, inter, lo, hi, X0, lane, ubase, dbase, slab_w, jy, jy * key_stride);
             } else {
-                run_item<B, NDY, 1, PITCH, 1, K64, RB>(a, active, j, dyg, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
+                run_item<B, NDY, 1, PITCH, 1, K64, RB>(a, active, j, dyi0, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
                                                        s_key, tile_interior, dyi_lo, dyi_hi, X0, lane, ubase, dbase, slab_w);
             }
         }
