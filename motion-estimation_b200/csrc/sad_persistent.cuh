@@ -36,7 +36,7 @@ struct UnitInfo {                  // one per stage: written by the producer, re
     int pair, tile_id, tx, ty, prev_slot, cur_slot;
     int X0, Y0, nj, nblk;
     int ubase, dbase, slab_w, lastx;
-    int dyi_lo, dyi_hi, tile_interior, dyg_lo, nd, dy_cap;
+    int dyi_lo, dyi_hi, tile_interior, nd, dy_cap;
     int n_wide, n_narrow, per_j_w, per_j_n, total_w, total_n;
     unsigned magic_pjw, magic_pjn;
     int chunks_w, chunks_n;        // 32-item chunks of wide / narrow patches
@@ -104,9 +104,8 @@ __device__ __forceinline__ UnitInfo decode_unit(const SearchArgs &a, int u)
     const int xlast = ui.X0 + (ui.nblk - 1) * B;
     ui.tile_interior = ui.dyi_lo == 0 && ui.dyi_hi == slab_h - 1 && a.R - ui.X0 - ui.ubase <= 0 &&
                        min(twoR, a.R + a.W - B - xlast) - ui.ubase >= ui.slab_w - 1;
-    ui.dyg_lo = ui.dyi_lo / NDY;
-    ui.dy_cap = max(0, slab_h - NDY);               // see sad_search_kernel: the last dy group does not hang over the slab
-    ui.nd = ui.dyi_hi >= ui.dyi_lo ? ui.dyi_hi / NDY - ui.dyg_lo + 1 : 0;
+    ui.dy_cap = max(ui.dyi_hi - NDY + 1, 0);        // see sad_search_kernel: groups start at dyi_lo, the last one ends at dyi_hi
+    ui.nd = ui.dyi_hi >= ui.dyi_lo ? (ui.dyi_hi - ui.dyi_lo) / NDY + 1 : 0;
     ui.n_wide = a.n_wide[ui.lastx];
     ui.n_narrow = a.n_narrow[ui.lastx];
     ui.per_j_w = ui.nd * ui.n_wide;
@@ -358,7 +357,7 @@ sad_search_persistent(const __grid_constant__ CUtensorMap tm_win, const __grid_c
                     const bool active = w_raw < total;
                     const int w = active ? w_raw : total - 1;
                     const int j = fastdiv(w, ui.magic_pjw), r = w - j * per_j;
-                    const int dq = fastdiv(r, a.magic_nw[ui.lastx]), cg = r - dq * n_wide, dyi0 = min((ui.dyg_lo + dq) * NDY, ui.dy_cap);
+                    const int dq = fastdiv(r, a.magic_nw[ui.lastx]), cg = r - dq * n_wide, dyi0 = min(ui.dyi_lo + dq * NDY, ui.dy_cap);
                     const unsigned g = grp[cg];
                     run_item<B, NDY, NQ, PITCH, LWW, K64, RB>(a, active, j, dyi0, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
                                                               skeys, ui.tile_interior != 0, ui.dyi_lo, ui.dyi_hi, ui.X0, lane,
@@ -368,7 +367,7 @@ sad_search_persistent(const __grid_constant__ CUtensorMap tm_win, const __grid_c
                     const bool active = w_raw < total;
                     const int w = active ? w_raw : total - 1;
                     const int j = fastdiv(w, ui.magic_pjn), r = w - j * per_j;
-                    const int dq = fastdiv(r, a.magic_nn[ui.lastx]), cg = r - dq * n_narrow, dyi0 = min((ui.dyg_lo + dq) * NDY, ui.dy_cap);
+                    const int dq = fastdiv(r, a.magic_nn[ui.lastx]), cg = r - dq * n_narrow, dyi0 = min(ui.dyi_lo + dq * NDY, ui.dy_cap);
                     const unsigned g = grp[ui.n_wide + cg];
                     run_item<B, NDY, 1, PITCH, 1, K64, RB>(a, active, j, dyi0, (int)(g >> 12), (int)(g & 0xfffu), s_win, s_ref,
                                                            skeys, ui.tile_interior != 0, ui.dyi_lo, ui.dyi_hi, ui.X0, lane,

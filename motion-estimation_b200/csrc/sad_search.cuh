@@ -652,12 +652,12 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     const int xlast = X0 + (nblk - 1) * B;
     const bool x_interior = a.R - X0 - ubase <= 0 && min(twoR, a.R + a.W - B - xlast) - ubase >= slab_w - 1;
     const bool tile_interior = x_interior && a.R - Y0 - dbase <= 0 && min(twoR, a.R + a.H - B - Ylast) - dbase >= slab_h - 1;
-    const int dyg_lo = dyi_lo / NDY, dyg_hi = dyi_hi >= 0 ? dyi_hi / NDY : -1;
-    // The last dy group of a slab whose height is not a multiple of NDY starts NDY rows before the slab's end instead of
-    // hanging over it: its first rows repeat candidates of the group before (same keys, harmless for the argmin), and
-    // the group stays on the test-free argmin path instead of carrying masked rows (a quarter of all items at +-8).
-    const int dy_cap = max(0, slab_h - NDY);
-    const int nd = dyi_hi >= dyi_lo ? dyg_hi - dyg_lo + 1 : 0;         // 0: this slab holds no candidate of this block row
+    // dy groups are laid from the first valid row (dyi_lo) in steps of NDY; the last one starts NDY rows before the last
+    // valid row instead of hanging over it.  Its first rows then repeat candidates of the group before (same keys, harmless
+    // for the argmin), and every group lies inside the valid range: no masked rows, test-free argmin path -- also for the
+    // block rows at the top and bottom of the frame (all rows of the 64-pixel-tall recordings).
+    const int dy_cap = max(dyi_hi - NDY + 1, 0);
+    const int nd = dyi_hi >= dyi_lo ? (dyi_hi - dyi_lo) / NDY + 1 : 0; // 0: this slab holds no candidate of this block row
     if (tid < kMaxTileKeys) s_key[tid] = kNone;
 
     const int wx0 = X0 - a.R - a.x_off + ubase, wy0 = Y0 - a.R + dbase;   // wx0 is a multiple of 16 (su is)
@@ -769,7 +769,7 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
             const int w = active ? w_raw : total - 1;
             const int j = fastdiv(w, magic_pj), r = w - j * per_j;
             const int dq = fastdiv(r, a.magic_nw[lastx]), cg = r - dq * n_wide;                       // column group varies fastest across lanes
-            const int dyi0 = min((dyg_lo + dq) * NDY, dy_cap);
+            const int dyi0 = min(dyi_lo + dq * NDY, dy_cap);
             const unsigned g = grp[cg];
             if constexpr (MR) {
                 int jx, jy, lo, hi; bool inter;
@@ -794,7 +794,7 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
             const int w = active ? w_raw : total - 1;
             const int j = fastdiv(w, magic_pj), r = w - j * per_j;
             const int dq = fastdiv(r, a.magic_nn[lastx]), cg = r - dq * n_narrow;
-            const int dyi0 = min((dyg_lo + dq) * NDY, dy_cap);
+            const int dyi0 = min(dyi_lo + dq * NDY, dy_cap);
             const unsigned g = grp[n_wide + cg];
             if constexpr (MR) {
                 int jx, jy, lo, hi; bool inter;
