@@ -169,6 +169,7 @@ struct me_ctx {
     CUtensorMap tm_win{}, tm_ref{};
     KernelChoice kc{};
     int threads = 0, smem = 0, sm_count = 0, win_pitch = 0;
+    bool force_persistent = false;                // ME_PERSISTENT=2: also for launches of a few units (tests)
     int pstage_bytes = 0, smem_persistent = 0;    // resident kernel: one stage of window copies, total dynamic smem (0 = not usable)
     int *d_ready = nullptr, *d_error = nullptr;  // resident kernel: queue of completed pairs, wait-timeout flag
     int64_t launches = 0;
@@ -342,6 +343,7 @@ int configure(me_ctx *c)
     c->pstage_bytes = round_up(a.n_bufs * a.copy_bytes + 128 + 256 + me::kRefPitch * B, 128);
     c->smem_persistent = me::kStages * c->pstage_bytes + (2 * me::kSelBins + 64) * 4 + 1024;
     if (c->smem_persistent > 227 * 1024 || !c->kc.fn_persistent || env_int("ME_PERSISTENT", 1) == 0) c->smem_persistent = 0;
+    c->force_persistent = env_int("ME_PERSISTENT", 1) == 2;
     if (c->smem_persistent && env_int("ME_PERSISTENT", 1) != 2) {
         // The resident kernel pays when searching a unit (tile x slab) takes the consumer warps clearly longer than
         // loading and shifting its window takes the producers; the realigning copy build of windows whose origin is
@@ -405,7 +407,7 @@ int launch_search(me_ctx *c, const uint8_t *frames, const CUtensorMap &tm_win, c
     a.pairs = c->d_pairs;
     const long long units = (long long)a.tiles_per_pair * n_pairs * a.nsx * a.nsy;
     CU_TRY(cudaEventRecord(c->ev_k0, st));
-    if (c->smem_persistent && units >= 2ll * c->sm_count) {
+    if (c->smem_persistent && (units >= 2ll * c->sm_count || c->force_persistent)) {
         // enough work to keep one resident CTA per SM busy: the warp-specialised kernel (sad_persistent.cuh)
         me::PersistArgs pa;
         pa.n_units = (int)units; pa.n_pairs = n_pairs; pa.stage_bytes = c->pstage_bytes;

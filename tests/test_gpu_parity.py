@@ -52,6 +52,31 @@ def test_search_equals_oracle(me, H, W, B, R):
             check_pair(est, i, frames[a], frames[c], cfg, res[i])
 
 
+RESIDENT_CASES = [(64, 640, 16, 32), (270, 480, 16, 32), (136, 256, 8, 64), (96, 160, 32, 16), (64, 128, 32, 40), (128, 128, 16, 96),
+                  (160, 192, 16, 100), (72, 136, 8, 90), (200, 168, 32, 72), (144, 320, 16, 128), (80, 304, 8, 128), (40, 336, 8, 7)]
+
+
+@pytest.mark.parametrize("H,W,B,R", RESIDENT_CASES)
+def test_resident_kernel_equals_oracle(me, monkeypatch, H, W, B, R):
+    """The warp-specialised one-CTA-per-SM kernel forced on small launches: single-slab, slabbed and 64-bit-key plans,
+    every block size, shifted and unshifted window origins; twice, so tickets, queues and counters must be left clean."""
+    from motion_estimation_b200 import synth
+    monkeypatch.setenv("ME_PERSISTENT", "2")
+    monkeypatch.setenv("ME_TMR", "1")                   # the resident kernel takes one block row per unit
+    n = 4
+    frames, _ = synth.translating_frames(n, H, W, min(R, 24))
+    cfg = me.SearchConfig(block=B, range=R)
+    with me.MotionEstimator(H, W, cfg, max_frames=n, max_pairs=n + 1) as est:
+        if not est.geometry["resident_kernel"]:
+            pytest.skip("two stages of this plan do not fit in shared memory")
+        est.upload(frames)
+        pairs = [(0, 1), (1, 2), (2, 3), (3, 0), (2, 2)]
+        for _ in range(2):
+            res = est.search(pairs)
+            for i, (a, c) in enumerate(pairs):
+                check_pair(est, i, frames[a], frames[c], cfg, res[i])
+
+
 @pytest.mark.parametrize("kw", [dict(subpixel=False), dict(min_range=60), dict(min_curv=400), dict(min_valid=10 ** 6)])
 def test_gates_and_modes_equal_oracle(me, kw):
     from motion_estimation_b200 import synth
