@@ -169,6 +169,8 @@ struct me_ctx {
     CUtensorMap tm_win{}, tm_ref{};
     KernelChoice kc{};
     int threads = 0, smem = 0, sm_count = 0, win_pitch = 0;
+    int plan_pairs = 1;                           // pairs per launch the tile shape is planned for (small frames: enough CTAs)
+    me_ctx *big = nullptr;                        // second plan for launches of many pairs (plan fields + tensor maps only)
     bool force_persistent = false;                // ME_PERSISTENT=2: also for launches of a few units (tests)
     int pstage_bytes = 0, smem_persistent = 0;    // resident kernel: one stage of window copies, total dynamic smem (0 = not usable)
     int *d_ready = nullptr, *d_error = nullptr;  // resident kernel: queue of completed pairs, wait-timeout flag
@@ -249,9 +251,9 @@ int configure(me_ctx *c)
                 if (tmb < 1) continue;
                 // small frames: keep at least ~2 CTAs per SM in flight for a 4-pair batch
                 if (tmr > 1 && !forced_tmr &&
-                    (long long)ceil_div(a.nmbx, tmb) * ceil_div(a.nby, tmr) * (c->max_pairs > 4 ? 4 : c->max_pairs) < 2ll * c->sm_count) continue;
+                    (long long)ceil_div(a.nmbx, tmb) * ceil_div(a.nby, tmr) * c->plan_pairs < 2ll * c->sm_count) continue;
                 if (!forced_tmb)
-                    while (tmb > 1 && (long long)ceil_div(a.nmbx, tmb) * ceil_div(a.nby, tmr) * nsx * nsy * (c->max_pairs > 4 ? 4 : c->max_pairs) < 2ll * c->sm_count) --tmb;
+                    while (tmb > 1 && (long long)ceil_div(a.nmbx, tmb) * ceil_div(a.nby, tmr) * nsx * nsy * c->plan_pairs < 2ll * c->sm_count) --tmb;
                 // every tile width from the widest that fits down to half of it: a narrower tile can
                 // divide its work items over the CTA's warps more evenly (r01: 8 blocks beat 9 by 1.2 %)
                 const int tmb_lo = forced_tmb ? tmb : (tmb + 1) / 2;
@@ -399,27 +401,38 @@ int configure(me_ctx *c)
     return ME_OK;
 }
 
-int launch_search(me_ctx *c, const uint8_t *frames, const CUtensorMap &tm_win, const CUtensorMap &tm_ref,
-                  int n_pairs, cudaStream_t st)
+// The plan a launch of n_pairs runs with: the context's own (tiles small enough to fill the GPU with a few pairs), or
+// the one made for max_pairs when the launch is large enough to fill the GPU with its bigger tiles.
+const me_ctx *pick_plan(const me_ctx *c, int n_pairs)
 {
-    me::SearchArgs a = c->args;
+    if (c->big && (long long)c->big->args.tiles_per_pair * c->big->args.nsx * c->big->args.nsy * n_pairs >= 2ll * c->sm_count)
+        return c->big;
+    return c;
+}
+
+// pl: the plan (c itself or c->big); frame_pitch 0 = the context's ring layout.
+int launch_search(me_ctx *c, const me_ctx *pl, const uint8_t *frames, const CUtensorMap &tm_win, const CUtensorMap &tm_ref,
+                  int n_pairs, cudaStream_t st, size_t frame_pitch = 0)
+{
+    me::SearchArgs a = pl->args;
     a.frames = frames;
     a.pairs = c->d_pairs;
+    if (frame_pitch) { a.frame_pitch = (int)frame_pitch; a.frame_stride = (long long)frame_pitch * c->H; }
     const long long units = (long long)a.tiles_per_pair * n_pairs * a.nsx * a.nsy;
     CU_TRY(cudaEventRecord(c->ev_k0, st));
-    if (c->smem_persistent && (units >= 2ll * c->sm_count || c->force_persistent)) {
+    if (pl->smem_persistent && (units >= 2ll * c->sm_count || pl->force_persistent)) {
         // enough work to keep one resident CTA per SM busy: the warp-specialised kernel (sad_persistent.cuh)
         me::PersistArgs pa;
-        pa.n_units = (int)units; pa.n_pairs = n_pairs; pa.stage_bytes = c->pstage_bytes;
+        pa.n_units = (int)units; pa.n_pairs = n_pairs; pa.stage_bytes = pl->pstage_bytes;
         pa.ready_pairs = c->d_ready; pa.error_flag = c->d_error;
         CU_TRY(cudaMemsetAsync(c->d_ready, 0xff, sizeof(int) * (size_t)(n_pairs + 2), st));   // pair queue + unit counter
         void *params[4] = {(void *)&tm_win, (void *)&tm_ref, (void *)&a, (void *)&pa};
         const unsigned grid = units < c->sm_count ? (unsigned)units : (unsigned)c->sm_count;
-        CU_TRY(cudaLaunchKernel(c->kc.fn_persistent, dim3(grid), dim3((unsigned)c->kc.persist_threads), params,
-                                (size_t)c->smem_persistent, st));
+        CU_TRY(cudaLaunchKernel(pl->kc.fn_persistent, dim3(grid), dim3((unsigned)pl->kc.persist_threads), params,
+                                (size_t)pl->smem_persistent, st));
     } else {
         void *params[3] = {(void *)&tm_win, (void *)&tm_ref, (void *)&a};
-        CU_TRY(cudaLaunchKernel(c->kc.fn, dim3((unsigned)units), dim3((unsigned)c->threads), params, (size_t)c->smem, st));
+        CU_TRY(cudaLaunchKernel(pl->kc.fn, dim3((unsigned)units), dim3((unsigned)pl->threads), params, (size_t)pl->smem, st));
     }
     CU_TRY(cudaEventRecord(c->ev_k1, st));
     c->launches += 1;
@@ -569,8 +582,23 @@ int me_create(int device, int height, int width, const me_params *params, int ma
     c->sm_count = prop.multiProcessorCount;
     c->pitch = (size_t)round_up(width, 16);
     c->frame_stride = c->pitch * (size_t)height;
+    c->plan_pairs = max_pairs > 4 ? 4 : max_pairs;      // small frames: tiles small enough that a few pairs fill the GPU
     int rc = configure(c);
     if (rc) { delete c; return rc; }
+    if (max_pairs > 4) {
+        // ... and a second plan for launches of many pairs, where bigger tiles fill it as well (the 640x64 recordings: 2-block
+        // tiles for 4 pairs, 8-block tiles for 64).  Kept only when it differs.
+        me_ctx *b = new me_ctx();
+        b->device = device; b->H = height; b->W = width; b->p = *params;
+        b->max_frames = max_frames; b->max_pairs = max_pairs; b->sm_count = c->sm_count;
+        b->pitch = c->pitch; b->frame_stride = c->frame_stride;
+        b->plan_pairs = max_pairs;
+        const me::SearchArgs &x = c->args, &y = b->args;
+        if (configure(b) == ME_OK && (x.tmb != y.tmb || x.tmr != y.tmr || c->win_pitch != b->win_pitch || x.nsx != y.nsx || x.nsy != y.nsy))
+            c->big = b;
+        else
+            delete b;
+    }
 
 #define CREATE_TRY(expr)                                                                                     \
     do {                                                                                                     \
@@ -615,8 +643,9 @@ int me_create(int device, int height, int width, const me_params *params, int ma
     CREATE_TRY(cudaMalloc(&c->args.pair_out, sizeof(me_pair_result) * (size_t)max_pairs));
     CREATE_TRY(cudaMalloc(&c->args.pair_ticket, sizeof(unsigned) * (size_t)max_pairs));
     CREATE_TRY(cudaMemset(c->args.pair_ticket, 0, sizeof(unsigned) * (size_t)max_pairs));
-    if (c->args.nsx * c->args.nsy > 1) {          // cross-slab argmin scratch: all-ones keys, zero tickets (self-restoring)
-        const size_t nt = (size_t)c->args.tiles_per_pair * (size_t)max_pairs;
+    const bool big_slabs = c->big && c->big->args.nsx * c->big->args.nsy > 1;
+    if (c->args.nsx * c->args.nsy > 1 || big_slabs) {   // cross-slab argmin scratch: all-ones keys, zero tickets (self-restoring)
+        const size_t nt = (size_t)std::max(c->args.tiles_per_pair, c->big ? c->big->args.tiles_per_pair : 0) * (size_t)max_pairs;
         CREATE_TRY(cudaMalloc(&c->args.blk_key, nb * sizeof(unsigned long long)));
         CREATE_TRY(cudaMemset(c->args.blk_key, 0xff, nb * sizeof(unsigned long long)));
         CREATE_TRY(cudaMalloc(&c->args.tile_ticket, nt * sizeof(unsigned)));
@@ -631,9 +660,24 @@ int me_create(int device, int height, int width, const me_params *params, int ma
     }
     CREATE_TRY(cudaFuncSetAttribute(c->kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, c->smem));
     CREATE_TRY(cudaFuncSetAttribute(c->kc.fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    if (me_ctx *b = c->big) {                            // same outputs and scratch, its own kernels and launch shape
+        b->args.blk_mv = c->args.blk_mv; b->args.blk_sad = c->args.blk_sad; b->args.blk_sub = c->args.blk_sub;
+        b->args.blk_flags = c->args.blk_flags; b->args.pair_out = c->args.pair_out; b->args.pair_ticket = c->args.pair_ticket;
+        b->args.blk_key = c->args.blk_key; b->args.tile_ticket = c->args.tile_ticket;
+        if (b->smem_persistent) {
+            CREATE_TRY(cudaFuncSetAttribute(b->kc.fn_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, b->smem_persistent));
+            CREATE_TRY(cudaFuncSetAttribute(b->kc.fn_persistent, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        }
+        CREATE_TRY(cudaFuncSetAttribute(b->kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, b->smem));
+        CREATE_TRY(cudaFuncSetAttribute(b->kc.fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    }
 #undef CREATE_TRY
     rc = make_tensor_map(&c->tm_win, c->d_frames, c->W, c->H, max_frames, c->pitch, c->win_pitch, c->args.box_rows);
     if (!rc) rc = make_tensor_map(&c->tm_ref, c->d_frames, c->W, c->H, max_frames, c->pitch, me::kRefPitch, B * c->args.tmr);
+    if (!rc && c->big) {
+        rc = make_tensor_map(&c->big->tm_win, c->d_frames, c->W, c->H, max_frames, c->pitch, c->big->win_pitch, c->big->args.box_rows);
+        if (!rc) rc = make_tensor_map(&c->big->tm_ref, c->d_frames, c->W, c->H, max_frames, c->pitch, me::kRefPitch, B * c->big->args.tmr);
+    }
     if (rc) { me_destroy(c); return rc; }
     *out = c;
     return ME_OK;
@@ -649,6 +693,8 @@ int me_destroy(me_ctx *c)
     cudaFree(c->args.blk_mv); cudaFree(c->args.blk_sad); cudaFree(c->args.blk_sub); cudaFree(c->args.blk_flags);
     cudaFree(c->args.pair_out); cudaFree(c->args.pair_ticket); cudaFree(c->args.blk_key); cudaFree(c->args.tile_ticket);
     cudaFree(c->d_ready); cudaFree(c->d_error);
+    delete c->big;                                       // owns nothing: its pointers are the context's
+    c->big = nullptr;
     for (int i = 0; i < 2; ++i) {
         if (c->h_stage[i]) cudaFreeHost(c->h_stage[i]);
         if (c->stage_free[i]) cudaEventDestroy(c->stage_free[i]);
@@ -855,7 +901,8 @@ int me_search(me_ctx *c, const int32_t *pairs, int n_pairs)
     memcpy(c->h_pairs, pairs, sizeof(int32_t) * 2 * (size_t)n_pairs);
     CU_TRY(cudaMemcpyAsync(c->d_pairs, c->h_pairs, sizeof(int32_t) * 2 * (size_t)n_pairs, cudaMemcpyHostToDevice, c->s_compute));
     if (c->have_upload) CU_TRY(cudaStreamWaitEvent(c->s_compute, c->ev_upload, 0));
-    rc = launch_search(c, c->d_frames, c->tm_win, c->tm_ref, n_pairs, c->s_compute);
+    const me_ctx *pl = pick_plan(c, n_pairs);
+    rc = launch_search(c, pl, c->d_frames, pl->tm_win, pl->tm_ref, n_pairs, c->s_compute);
     if (rc) return rc;
     CU_TRY(cudaEventRecord(c->ev_search, c->s_compute));
     {
@@ -881,20 +928,15 @@ int me_search_device(me_ctx *c, const uint8_t *d_frames, size_t pitch, int n_fra
     if (rc) return rc;
     CU_TRY(cudaSetDevice(c->device));
     cudaStream_t st = stream ? (cudaStream_t)stream : c->s_compute;
+    const me_ctx *pl = pick_plan(c, n_pairs);
     CUtensorMap tw, tr;
-    rc = make_tensor_map(&tw, d_frames, c->W, c->H, n_frames, pitch, c->win_pitch, c->args.box_rows);
-    if (!rc) rc = make_tensor_map(&tr, d_frames, c->W, c->H, n_frames, pitch, me::kRefPitch, c->p.block * c->args.tmr);
+    rc = make_tensor_map(&tw, d_frames, c->W, c->H, n_frames, pitch, pl->win_pitch, pl->args.box_rows);
+    if (!rc) rc = make_tensor_map(&tr, d_frames, c->W, c->H, n_frames, pitch, me::kRefPitch, c->p.block * pl->args.tmr);
     if (rc) return rc;
     if (c->have_search) CU_TRY(cudaEventSynchronize(c->ev_search));
     memcpy(c->h_pairs, pairs, sizeof(int32_t) * 2 * (size_t)n_pairs);
     CU_TRY(cudaMemcpyAsync(c->d_pairs, c->h_pairs, sizeof(int32_t) * 2 * (size_t)n_pairs, cudaMemcpyHostToDevice, st));
-    const int keep_pitch = c->args.frame_pitch;
-    const long long keep_stride = c->args.frame_stride;
-    c->args.frame_pitch = (int)pitch;
-    c->args.frame_stride = (long long)pitch * c->H;
-    rc = launch_search(c, d_frames, tw, tr, n_pairs, st);
-    c->args.frame_pitch = keep_pitch;
-    c->args.frame_stride = keep_stride;
+    rc = launch_search(c, pl, d_frames, tw, tr, n_pairs, st, pitch);
     if (rc) return rc;
     CU_TRY(cudaEventRecord(c->ev_search, st));
     if (st != c->s_compute) CU_TRY(cudaStreamWaitEvent(c->s_compute, c->ev_search, 0));
@@ -1105,7 +1147,7 @@ extern "C" int me_search_static_scratch(const uint8_t *d_frames, size_t pitch, i
     // Launch shape: the same planner the contexts use, run on a throw-away host-side description.
     me_ctx plan;
     plan.device = dev; plan.H = height; plan.W = width; plan.p = *params;
-    plan.max_frames = n_frames; plan.max_pairs = n_pairs;
+    plan.max_frames = n_frames; plan.max_pairs = n_pairs; plan.plan_pairs = n_pairs;
     plan.sm_count = g_static_dev[dev].sm_count;
     plan.pitch = pitch; plan.frame_stride = pitch * (size_t)height;
     rc = configure(&plan);
