@@ -356,7 +356,7 @@ int configure(me_ctx *c)
         const double cand = (double)U * U / (a.nsx * a.nsy);                                             // candidates of an average slab
         const double t_cons = (double)a.tmb * NSUB * cand * B * B / 256.0;                               // cycles at 64 lanes x 4 px
         const double build = (double)a.n_row_boxes * a.box_rows * (c->win_pitch / 16) / 32.0 * 120.0 / me::kProducerWarps;
-        const double t_prod = 6000.0 + build * (a.x_off ? 3.0 : 1.0);
+        const double t_prod = 6000.0 + build * (a.x_off == 0 ? 1.0 : (a.x_off & 3) ? 3.0 : 1.5);   // whole-word offsets skip the selects
         if (t_cons < 1.7 * t_prod) c->smem_persistent = 0;
     }
     if (a.tmr > 1) c->smem_persistent = 0;          // the resident kernel takes one block row per unit

@@ -303,6 +303,21 @@ sad_search_persistent(const __grid_constant__ CUtensorMap tm_win, const __grid_c
                             *reinterpret_cast<uint4 *>(s_win + (size_t)sft * (a.copy_bytes + kCopySkew) + 16 * (size_t)i) = o;
                         }
                     }
+                } else if ((a.x_off & 3) == 0) {                          // see sad_search_kernel: whole-word offset, no selects
+                    const uint32_t *rawo = raw + (a.x_off >> 2);
+                    for (int i = warp * 32 + lane; i < chunks; i += 32 * NP) {
+                        const uint32_t e0 = rawo[4 * i], e1 = rawo[4 * i + 1], e2 = rawo[4 * i + 2], e3 = rawo[4 * i + 3], e4 = rawo[4 * i + 4];
+                        *reinterpret_cast<uint4 *>(s_win + 16 * (size_t)i) = make_uint4(e0, e1, e2, e3);
+#pragma unroll
+                        for (int sft = 1; sft < 4; ++sft) {
+                            uint4 o;
+                            o.x = __funnelshift_r(e0, e1, 8 * sft);
+                            o.y = __funnelshift_r(e1, e2, 8 * sft);
+                            o.z = __funnelshift_r(e2, e3, 8 * sft);
+                            o.w = __funnelshift_r(e3, e4, 8 * sft);
+                            *reinterpret_cast<uint4 *>(s_win + (size_t)sft * (a.copy_bytes + kCopySkew) + 16 * (size_t)i) = o;
+                        }
+                    }
                 } else {
                     for (int i = warp * 32 + lane; i < chunks; i += 32 * NP) {
                         uint32_t w[9];

@@ -713,6 +713,23 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
                     *reinterpret_cast<uint4 *>(s_win + (size_t)s * (a.copy_bytes + kCopySkew) + 16 * (size_t)i) = o;
                 }
             }
+        } else if ((a.x_off & 3) == 0) {
+            // window origin a whole number of words off the aligned one (even ranges: +-8, +-24, +-40): copy s is the raw
+            // row from word x_off/4 on, funnel-shifted by s bytes -- no per-word selects
+            const uint32_t *rawo = raw + (a.x_off >> 2);
+            for (int i = tid; i < chunks; i += blockDim.x) {
+                const uint32_t e0 = rawo[4 * i], e1 = rawo[4 * i + 1], e2 = rawo[4 * i + 2], e3 = rawo[4 * i + 3], e4 = rawo[4 * i + 4];
+                *reinterpret_cast<uint4 *>(s_win + 16 * (size_t)i) = make_uint4(e0, e1, e2, e3);
+#pragma unroll
+                for (int s = 1; s < 4; ++s) {
+                    uint4 o;
+                    o.x = __funnelshift_r(e0, e1, 8 * s);
+                    o.y = __funnelshift_r(e1, e2, 8 * s);
+                    o.z = __funnelshift_r(e2, e3, 8 * s);
+                    o.w = __funnelshift_r(e3, e4, 8 * s);
+                    *reinterpret_cast<uint4 *>(s_win + (size_t)s * (a.copy_bytes + kCopySkew) + 16 * (size_t)i) = o;
+                }
+            }
         } else {
             for (int i = tid; i < chunks; i += blockDim.x) {
                 uint32_t w[9];
