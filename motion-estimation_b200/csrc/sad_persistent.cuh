@@ -24,7 +24,10 @@
 namespace me {
 
 constexpr int kStages = 2;
-constexpr int kConsumerWarps = 20;        // 8/16-pixel blocks (80 registers per thread)
+#ifndef ME_CW
+#define ME_CW 20
+#endif
+constexpr int kConsumerWarps = ME_CW;        // 8/16-pixel blocks (80 registers per thread)
 constexpr int kConsumerWarps32 = 16;      // 32-pixel blocks: the patch needs ~110 registers
 #ifndef ME_NP
 #define ME_NP 2
