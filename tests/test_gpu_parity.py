@@ -289,3 +289,36 @@ def test_4k_properties(me):
         for i, (dx, dy) in enumerate(shifts):
             assert res[i]["flag"] == 1 and res[i]["pdx"] == dx and res[i]["pdy"] == dy
         _sample_blocks_equal_oracle(est, 1, frames[1], frames[2], 8, 64, [(0, 0), (479, 269), (240, 135), (7, 262)])
+
+
+def _fuzz_case(seed):
+    """A seeded random geometry: frame size (ragged against every block size), block, range (aligned and unaligned window
+    origins, slabbed and 64-bit-key ranges now and then), batch size (small and large launches take different plans)."""
+    rng = np.random.default_rng(1000 + seed)
+    B = int(rng.choice([8, 16, 32]))
+    R = int(rng.choice([1, 3, 6, 8, 11, 16, 17, 24, 28, 32, 33, 40, 48, 57, 64, 80, 100, 128]))
+    H = int(rng.integers(B, 7 * B + 1)) if R > 48 else int(rng.integers(B, 12 * B + 1))
+    W = int(rng.integers(B, 10 * B + 1)) if R > 48 else int(rng.integers(B, 40 * B + 1))
+    n_pairs = int(rng.choice([1, 2, 5, 24]))
+    mode = int(rng.integers(0, 3))          # 0 default plan, 1 resident kernel forced, 2 one CTA per tile forced
+    kw = dict(subpixel=bool(rng.integers(0, 2)), min_range=int(rng.choice([0, 2, 30])), min_curv=int(rng.choice([1, 50])))
+    return H, W, B, R, n_pairs, mode, kw
+
+
+@pytest.mark.parametrize("seed", range(40))
+def test_random_geometries_equal_oracle(me, monkeypatch, seed):
+    from motion_estimation_b200 import synth
+    H, W, B, R, n_pairs, mode, kw = _fuzz_case(seed)
+    if mode:
+        monkeypatch.setenv("ME_PERSISTENT", "2" if mode == 1 else "0")
+    n = 4
+    frames, _ = synth.translating_frames(n, H, W, min(R, 20), seed_texture=seed, seed_motion=seed + 1)
+    cfg = me.SearchConfig(block=B, range=R, **kw)
+    rng = np.random.default_rng(seed)
+    pairs = [tuple(int(v) for v in rng.integers(0, n, 2)) for _ in range(n_pairs)]
+    with me.MotionEstimator(H, W, cfg, max_frames=n, max_pairs=max(n_pairs, 2)) as est:
+        est.upload(frames)
+        res = est.search(pairs)
+        for i in sorted(set(int(v) for v in rng.integers(0, n_pairs, 3))):      # the oracle runs on up to three pairs of the batch
+            a, c = pairs[i]
+            check_pair(est, i, frames[a], frames[c], cfg, res[i])
