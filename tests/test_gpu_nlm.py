@@ -101,3 +101,25 @@ def test_denoise_hf5_drop_in(me, golden_clips):
     assert len(short) == len(eq) - 4
     np.testing.assert_array_equal(short[7], _cv(eq_ref, 7, 9))
     api.close_engines()
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_shapes_equal_cv2(me, monkeypatch, seed):
+    """Seeded random frame sizes (below, around and above one 64x128 tile), windows, strengths and CTA splits."""
+    rng = np.random.default_rng(500 + seed)
+    H, W = int(rng.integers(16, 150)), int(rng.integers(16, 300))
+    tw, sw = int(rng.choice([7, 19])), int(rng.choice([11, 21, 41]))
+    h = float(rng.choice([4, 10, 15, 40]))
+    n = 5
+    windows = [1, int(rng.choice([1, 3])), int(rng.choice([3, 5])), int(rng.choice([0, 3])), 1]
+    split = int(rng.choice([0, 1, 2, 5]))
+    if split:
+        monkeypatch.setenv("ME_NLM_SPLIT", str(split))
+    frames = _noisy(n, H, W, seed, sigma=float(rng.choice([3, 10, 25])))
+    with me.MotionEstimator(max(H, 16), max(W, 16), me.SearchConfig(8, 4), max_frames=n, max_pairs=1) as est:
+        est.upload(frames)
+        est.denoise(0, windows, h, tw, sw)
+        got = est.download(0, n)
+    for k, T in enumerate(windows):
+        want = frames[k] if T == 0 else _cv(frames, k, T, h, tw, sw)
+        np.testing.assert_array_equal(got[k], want, err_msg=f"frame {k} window {T} ({H}x{W}, h={h}, {tw}/{sw}, split {split})")
