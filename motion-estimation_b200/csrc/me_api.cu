@@ -773,7 +773,7 @@ int me_clahe(me_ctx *c, int first_slot, int n_frames, double clip_limit, int til
         if (r.used && r.lo < first_slot + n_frames && r.hi >= first_slot) CU_TRY(cudaStreamWaitEvent(c->s_copy, r.done, 0));
     me::clahe_lut_kernel<<<dim3((unsigned)(tiles_x * tiles_y), (unsigned)n_frames), 256, 0, c->s_copy>>>(a, first_slot);
     CU_TRY(cudaGetLastError());
-    me::clahe_apply_kernel<<<dim3((unsigned)ceil_div(ceil_div(c->W, 4), 128), (unsigned)c->H, (unsigned)n_frames), 128, 0, c->s_copy>>>(a, first_slot);
+    me::clahe_apply_kernel<<<dim3((unsigned)ceil_div(c->H, me::kClaheRows), (unsigned)n_frames), 256, 0, c->s_copy>>>(a, first_slot);
     CU_TRY(cudaGetLastError());
     c->launches += 2;
     CU_TRY(cudaEventRecord(c->ev_upload, c->s_copy));   // same stream as the uploads: ordered after them, searches wait for this event
