@@ -25,7 +25,7 @@ def parse(argv=None):
     ap.add_argument("-d", nargs="?", dest="doLineDoubling", default="False", const="True",
                     help="accepted for compatibility; unused here as in the reference")
     ap.add_argument("--block", type=int, default=16)
-    ap.add_argument("--range", type=int, default=32, dest="search_range")
+    ap.add_argument("--range", type=int, default=64, dest="search_range")
     ap.add_argument("--device", type=int, default=0)
     ap.add_argument("--out", type=Path, default=None)
     return ap.parse_args(argv)

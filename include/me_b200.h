@@ -68,7 +68,11 @@ typedef struct me_pair_result {
     int32_t flag;           /* 1 = measurement accepted (the reference's measurement_flag)    */
     int32_t nvalid_x;       /* blocks that entered the x median                               */
     int32_t nvalid_y;
-    int32_t reserved;
+    int32_t n_textured;     /* blocks that passed the texture gate: nvalid_x / n_textured is the share of
+                               usable blocks with a strict interior minimum (low when the motion left +-R) */
+    float   mean_dx, mean_dy; /* frame mean of the valid blocks' refined displacements: the role of the
+                               reference's calculate_dense_flow (estimate_vel_vid.py:385-391, summed at
+                               :524-526), a by-product of the search                              */
 } me_pair_result;
 
 /* Static information about a context's geometry. */
@@ -136,6 +140,12 @@ int me_denoise(me_ctx *ctx, int first_slot, int n_frames, const int32_t *tempora
  * The reference keeps every stage's frames as (N,H,W) host arrays (estimate_vel_vid.py:215-219). */
 int me_download(me_ctx *ctx, uint8_t *luma, size_t row_pitch, int first_slot, int n_frames);
 
+/* The same towards device memory of this GPU (d_dst: n_frames x height rows of dst_pitch bytes): pre-processed frames
+ * go on to another GPU consumer -- e.g. the send buffer of the all_gather that reassembles a recording whose frame
+ * ranges were cleaned on different GPUs -- without passing through the host.  Ordered after the uploads / CLAHE /
+ * denoising issued so far; asynchronous on `stream` (NULL = the context's copy stream). */
+int me_copy_frames_device(me_ctx *ctx, void *d_dst, size_t dst_pitch, int first_slot, int n_frames, void *stream);
+
 /* Launch the search for n_pairs pairs of ring slots: pairs[2k] = previous frame, pairs[2k+1] =
  * current frame.  Asynchronous; results are read with me_fetch_*.  This is the call that replaces
  * the body of calc_ECC_transform for a whole batch. */
@@ -170,6 +180,37 @@ int64_t me_launch_count(const me_ctx *ctx);
  * start and stop.  me_timer_stop blocks until that work has finished. */
 int me_timer_start(me_ctx *ctx);
 int me_timer_stop(me_ctx *ctx, float *ms);
+
+/* The same stopwatch on the copy stream, where me_upload, me_clahe and me_denoise run. */
+int me_copy_timer_start(me_ctx *ctx);
+int me_copy_timer_stop(me_ctx *ctx, float *ms);
+
+/* The anchored pair walk of the video script -- the control flow of end_process, estimate_vel_vid.py:506-534 and
+ * :575 -- run inside the library so that no interpreter sits between two dependent searches.  Frame k is compared
+ * with the last ACCEPTED frame (the anchor), not with k-1: a pair is skipped, and the anchor kept, when
+ * pdx * scale < gate and flag == 1 (:531-534); otherwise frame k becomes the anchor (:575).
+ *
+ * Frames first_slot .. first_slot + n_frames - 1 of the ring are classified in order; the walk starts with the
+ * anchor in ring slot anchor_slot (any slot: the caller may keep an older anchor frame in a spare slot).  out[i]
+ * describes frame first_slot + i: the slot it was compared with, whether it was accepted, and the pair record of
+ * that comparison (full-resolution pixels).  Pairs are searched speculatively in batches (anchor, k), (anchor, k+1),
+ * ... sized from the distance of the last accept; d(anchor, k) does not depend on the batch it was computed in, so
+ * the result equals the one-pair-at-a-time loop.  scale: 0.5 for the reference's half-resolution unit, 1 for
+ * full-resolution pixels; gate: 2 in the reference.  searches / launches (may be NULL) count the work done.
+ * Returns after the last record is on the host. */
+typedef struct me_scan_record {
+    int32_t anchor_slot;
+    int32_t accepted;
+    me_pair_result pair;
+} me_scan_record;
+int me_anchored_scan(me_ctx *ctx, int anchor_slot, int first_slot, int n_frames, float scale, float gate,
+                     me_scan_record *out, int *searches, int *launches);
+
+/* Hand the per-pair records of the last search to another GPU consumer without a host bounce: copies n_pairs
+ * records from the context's result buffer to d_dst (device memory of the same GPU, e.g. the send buffer of an
+ * NCCL all_gather -- the one exchange step of the sharded path) on `stream`, ordered after the search.
+ * Asynchronous. */
+int me_copy_pair_records_device(me_ctx *ctx, void *d_dst, int n_pairs, void *stream);
 
 /* Integer-SAD issue-rate microbenchmark: runs a register-only VABSDIFF4 loop on every SM and
  * reports VABSDIFF4 thread-instructions per clock per SM and the SM clock it saw.  Used by bench.py

@@ -15,8 +15,8 @@ _CSRC = os.path.join(_HERE, "csrc")
 SO_PATH = os.path.join(_HERE, "libme_b200.so")
 HEADER = os.path.normpath(os.path.join(_HERE, "..", "include", "me_b200.h"))
 
-NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-              "-shared", "-Xcompiler", "-fPIC"]
+NVCC_COMPILE_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC"]
+NVCC_LINK_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-Xcompiler", "-fPIC"]
 
 
 class MEError(RuntimeError):
@@ -34,7 +34,12 @@ class Params(C.Structure):
 
 class PairResult(C.Structure):
     _fields_ = [("pdx", C.c_float), ("pdy", C.c_float), ("flag", C.c_int32),
-                ("nvalid_x", C.c_int32), ("nvalid_y", C.c_int32), ("reserved", C.c_int32)]
+                ("nvalid_x", C.c_int32), ("nvalid_y", C.c_int32), ("n_textured", C.c_int32),
+                ("mean_dx", C.c_float), ("mean_dy", C.c_float)]
+
+
+class ScanRecord(C.Structure):
+    _fields_ = [("anchor_slot", C.c_int32), ("accepted", C.c_int32), ("pair", PairResult)]
 
 
 class Geometry(C.Structure):
@@ -46,22 +51,58 @@ class Geometry(C.Structure):
                 ("window_pitch", C.c_int32), ("resident_kernel", C.c_int32), ("tile_blocks_y", C.c_int32)]
 
 
+INST_PITCHES = (144, 208, 240)
+INST_BLOCKS = (8, 16, 32)
+BUILD_DIR = os.path.join(_HERE, "build")
+
+
 def sources():
-    return [os.path.join(_CSRC, "me_api.cu"), os.path.join(_CSRC, "sad_search.cuh"), os.path.join(_CSRC, "clahe.cuh"), os.path.join(_CSRC, "nlm.cuh"), os.path.join(_CSRC, "sad_persistent.cuh"), HEADER]
+    names = ("me_api.cu", "search_inst.cu", "sad_search.cuh", "sad_persistent.cuh", "kernel_choice.h", "misc_kernels.cuh", "clahe.cuh", "nlm.cuh")
+    return [os.path.join(_CSRC, n) for n in names] + [HEADER]
+
+
+def _compile_jobs():
+    """(object file, nvcc arguments) per translation unit: the host side + small kernels, and the search kernels of
+    one (window pitch, block size) each, so that the build uses every core."""
+    jobs = [(os.path.join(BUILD_DIR, "me_api.o"), [os.path.join(_CSRC, "me_api.cu")])]
+    for p in INST_PITCHES:
+        for b in INST_BLOCKS:
+            jobs.append((os.path.join(BUILD_DIR, f"search_{p}_{b}.o"),
+                         [f"-DME_INST_PITCH={p}", f"-DME_INST_B={b}", os.path.join(_CSRC, "search_inst.cu")]))
+    return jobs
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    """Compile csrc/ for sm_100a with nvcc into libme_b200.so next to this file (in-tree)."""
+    """Compile csrc/ for sm_100a with nvcc into libme_b200.so next to this file (in-tree): ten translation units
+    in parallel, then one link."""
+    from concurrent.futures import ThreadPoolExecutor
     srcs = sources()
-    if not force and os.path.exists(SO_PATH) and all(os.path.getmtime(SO_PATH) >= os.path.getmtime(s) for s in srcs):
+    newest = max(os.path.getmtime(s) for s in srcs)
+    if not force and os.path.exists(SO_PATH) and os.path.getmtime(SO_PATH) >= newest:
         return SO_PATH
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
-    extra = os.environ.get("ME_NVCC_EXTRA", "").split()             # experiments only, e.g. -DME_SLICE16=1
-    cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO_PATH, srcs[0]]
+    extra = os.environ.get("ME_NVCC_EXTRA", "").split()             # experiments only, e.g. -DME_CW=16
     env = dict(os.environ)
     env.pop("CC", None)
     env.pop("CXX", None)
-    subprocess.run(cmd, check=True, env=env)
+    os.makedirs(BUILD_DIR, exist_ok=True)
+    stamp = os.path.join(BUILD_DIR, "flags.txt")
+    flags_now = " ".join(NVCC_COMPILE_FLAGS + extra)
+    if not os.path.exists(stamp) or open(stamp).read() != flags_now:
+        force = True
+
+    def compile_one(job):
+        obj, args = job
+        if not force and os.path.exists(obj) and os.path.getmtime(obj) >= newest:
+            return
+        cmd = [nvcc] + NVCC_COMPILE_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", obj] + args
+        subprocess.run(cmd, check=True, env=env)
+
+    jobs = _compile_jobs()
+    with ThreadPoolExecutor(max_workers=min(len(jobs), os.cpu_count() or 4)) as pool:
+        list(pool.map(compile_one, jobs))
+    open(stamp, "w").write(flags_now)
+    subprocess.run([nvcc] + NVCC_LINK_FLAGS + ["-o", SO_PATH] + [j[0] for j in jobs], check=True, env=env)
     return SO_PATH
 
 
@@ -103,12 +144,18 @@ def lib():
     L.me_launch_count.restype = C.c_int64
     L.me_microbench_vabsdiff4.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
                                           C.POINTER(C.c_int)]
+    L.me_copy_timer_start.argtypes = [vp]
+    L.me_copy_timer_stop.argtypes = [vp, C.POINTER(C.c_float)]
+    L.me_anchored_scan.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.me_copy_pair_records_device.argtypes = [vp, vp, C.c_int, vp]
+    L.me_copy_frames_device.argtypes = [vp, vp, C.c_size_t, C.c_int, C.c_int, vp]
     L.me_search_static_scratch.argtypes = [vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.POINTER(Params), i32p, C.c_int,
                                            vp, vp]
     L.me_search_static_scratch.restype = C.c_int
     for name in ("me_clahe", "me_denoise", "me_download", "me_create", "me_destroy", "me_get_geometry", "me_upload", "me_upload_bgr", "me_search",
                  "me_fetch_pairs", "me_fetch_blocks", "me_estimate_pair", "me_search_device", "me_sync",
-                 "me_last_search_ms", "me_microbench_vabsdiff4", "me_timer_start", "me_timer_stop"):
+                 "me_last_search_ms", "me_microbench_vabsdiff4", "me_timer_start", "me_timer_stop", "me_copy_timer_start",
+                 "me_copy_timer_stop", "me_anchored_scan", "me_copy_pair_records_device", "me_copy_frames_device"):
         getattr(L, name).restype = C.c_int
     _lib = L
     return L

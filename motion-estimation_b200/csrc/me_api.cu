@@ -11,6 +11,8 @@
 #include <string.h>
 #include <algorithm>
 #include <cmath>
+#include <mutex>
+#include <set>
 #include <string>
 #include <utility>
 #include <vector>
@@ -18,6 +20,8 @@
 #include "../../include/me_b200.h"
 #include "sad_search.cuh"
 #include "sad_persistent.cuh"
+#include "kernel_choice.h"
+#include "misc_kernels.cuh"
 #include "clahe.cuh"
 #include "nlm.cuh"
 
@@ -80,50 +84,48 @@ int make_tensor_map(CUtensorMap *tm, const uint8_t *base, int W, int H, int n_fr
     return ME_OK;
 }
 
-struct KernelChoice {
-    const void *fn = nullptr;
-    const void *fn_multirow = nullptr;     // the same kernel for tiles of several block rows
-    const void *fn_persistent = nullptr;   // warp-specialised resident form (32-bit keys only)
-    int ndy = 0, nq = 0, maxt = 0, pitch = 0, rank_bits = 0, persist_threads = 0;
-};
+using me::KernelChoice;
+using me::kNDY;
+using me::kNQ;
+using me::kMaxThreads;
+using me::kPitches;
 
-constexpr int kNDY = 5, kNQ = 4, kMaxThreads = 256;
-constexpr int kPitches[3] = {144, 208, 240};   // window row pitches built: odd multiples of 16 (bank-conflict free with NDY = 5)
-
-template <int B, int PITCH, bool K64, int RB>
-KernelChoice choice()
-{
-    KernelChoice k;
-    k.fn = (const void *)&me::sad_search_kernel<B, kNDY, kNQ, PITCH, K64, RB, kMaxThreads, 3, false>;
-    k.fn_multirow = (const void *)&me::sad_search_kernel<B, kNDY, kNQ, PITCH, K64, RB, kMaxThreads, 3, true>;
-    {
-        constexpr int CW = (B <= 16 && !K64) ? me::kConsumerWarps : me::kConsumerWarps32;
-        k.fn_persistent = (const void *)&me::sad_search_persistent<B, kNDY, kNQ, PITCH, K64, RB, CW, me::kProducerWarps>;
-        k.persist_threads = 32 * (me::kProducerWarps + CW);
-    }
-    k.ndy = kNDY; k.nq = kNQ; k.maxt = kMaxThreads; k.pitch = PITCH; k.rank_bits = RB;
-    return k;
-}
-
-template <int PITCH>
-KernelChoice pick_pitch(int B, bool k64)
-{
-    switch (B) {
-    case 8:  return k64 ? choice<8, PITCH, true, 32>() : choice<8, PITCH, false, 16>();     // sad < 2^14; rank < 2^16 unless R = 128
-    case 16: return k64 ? choice<16, PITCH, true, 32>() : choice<16, PITCH, false, 16>();   // sad < 2^16
-    default: return k64 ? choice<32, PITCH, true, 32>() : choice<32, PITCH, false, 14>();   // sad < 2^18
-    }
-}
-
-// One instantiation per (block size, window pitch, key width); see DESIGN.md "inner loop".
+// One instantiation per (block size, window pitch, key width), each pitch x block in its own translation unit
+// (search_inst.cu); see DESIGN.md "inner loop".
 KernelChoice pick_kernel(int B, int pitch, bool k64)
 {
-    switch (pitch) {
-    case 144: return pick_pitch<144>(B, k64);
-    case 208: return pick_pitch<208>(B, k64);
-    default:  return pick_pitch<240>(B, k64);
+#define ME_PICK(P)                                                                                   \
+    switch (B) {                                                                                     \
+    case 8:  return me::kernel_choice_##P##_8(k64);                                                  \
+    case 16: return me::kernel_choice_##P##_16(k64);                                                 \
+    default: return me::kernel_choice_##P##_32(k64);                                                 \
     }
+    switch (pitch) {
+    case 144: ME_PICK(144)
+    case 208: ME_PICK(208)
+    default:  ME_PICK(240)
+    }
+#undef ME_PICK
 }
+
+// A kernel's dynamic shared-memory limit belongs to the function and the device, not to a context: raise it once to the
+// opt-in maximum so that contexts (and the static-scratch path) with different window sizes that share an
+// instantiation cannot lower it under each other's launches.
+constexpr int kSmemOptInMax = 227 * 1024;
+int raise_smem_limit(const void *fn, bool prefer_smem = true)
+{
+    static std::mutex mu;
+    static std::set<std::pair<const void *, int>> done;
+    int dev = 0;
+    CU_TRY(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lock(mu);
+    if (done.count({fn, dev})) return ME_OK;
+    CU_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemOptInMax));
+    if (prefer_smem) CU_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    done.insert({fn, dev});
+    return ME_OK;
+}
+
 
 int env_int(const char *name, int dflt)
 {
@@ -156,6 +158,9 @@ struct me_ctx {
     cudaEvent_t ev_upload = nullptr, ev_search = nullptr, ev_k0 = nullptr, ev_k1 = nullptr;
     bool have_upload = false, have_search = false;
     cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;     // me_timer_start / me_timer_stop
+    cudaEvent_t ev_c0 = nullptr, ev_c1 = nullptr;     // me_copy_timer_start / me_copy_timer_stop
+    cudaEvent_t ev_rec = nullptr;                     // last me_copy_pair_records_device: the next search must not overwrite the records before it
+    bool have_rec = false;
     // the last few searches and the ring slots they read: an upload waits only for those it overwrites
     struct SearchRecord { int lo = 0, hi = -1; cudaEvent_t done = nullptr; bool used = false; };
     SearchRecord recent[4];
@@ -174,6 +179,7 @@ struct me_ctx {
     bool force_persistent = false;                // ME_PERSISTENT=2: also for launches of a few units (tests)
     int pstage_bytes = 0, smem_persistent = 0;    // resident kernel: one stage of window copies, total dynamic smem (0 = not usable)
     int *d_ready = nullptr, *d_error = nullptr;  // resident kernel: queue of completed pairs, wait-timeout flag
+    size_t n_tile_tickets = 0;                    // entries of args.tile_ticket (slabbed plans only)
     int64_t launches = 0;
     int64_t cand_px = 0, cand_px_valid = 0;
 };
@@ -419,6 +425,7 @@ int launch_search(me_ctx *c, const me_ctx *pl, const uint8_t *frames, const CUte
     a.pairs = c->d_pairs;
     if (frame_pitch) { a.frame_pitch = (int)frame_pitch; a.frame_stride = (long long)frame_pitch * c->H; }
     const long long units = (long long)a.tiles_per_pair * n_pairs * a.nsx * a.nsy;
+    if (c->have_rec) { CU_TRY(cudaStreamWaitEvent(st, c->ev_rec, 0)); c->have_rec = false; }
     CU_TRY(cudaEventRecord(c->ev_k0, st));
     if (pl->smem_persistent && (units >= 2ll * c->sm_count || pl->force_persistent)) {
         // enough work to keep one resident CTA per SM busy: the warp-specialised kernel (sad_persistent.cuh)
@@ -447,6 +454,21 @@ int check_pairs(me_ctx *c, const int32_t *pairs, int n_pairs, int n_frames)
         if (pairs[i] < 0 || pairs[i] >= n_frames)
             return fail(ME_EINVAL, "pair %d references frame %d, outside 0..%d", i / 2, pairs[i], n_frames - 1);
     return ME_OK;
+}
+
+// The resident kernel gave up waiting for a pair (its 2 s guard; never seen in a correct run, but a debugger, a
+// profiler replay or GPU time-slicing can stretch a launch that far).  The search that hit it is lost; the tickets
+// and keys it left half-counted are put back so that the context's next search starts clean.
+int report_search_timeout(me_ctx *c)
+{
+    const size_t nb = (size_t)c->args.nb * (size_t)c->max_pairs;
+    CU_TRY(cudaStreamSynchronize(c->s_compute));
+    CU_TRY(cudaMemset(c->args.pair_ticket, 0, sizeof(unsigned) * (size_t)c->max_pairs));
+    if (c->args.tile_ticket) CU_TRY(cudaMemset(c->args.tile_ticket, 0, c->n_tile_tickets * sizeof(unsigned)));
+    if (c->args.blk_key) CU_TRY(cudaMemset(c->args.blk_key, 0xff, nb * sizeof(unsigned long long)));
+    CU_TRY(cudaMemset(c->d_error, 0, sizeof(int)));
+    return fail(ME_ECUDA, "the resident search kernel gave up waiting for a frame pair to complete; the results of this "
+                          "search are invalid, the context has been reset and can be used again");
 }
 
 // Host rows -> pinned staging -> device slots, double-buffered on the copy stream.
@@ -544,7 +566,8 @@ void nlm_weight_table(float h, int tws, int sws, int n_frames, std::vector<int> 
 
 template <int TWS> int nlm_launch(const me::NlmArgs &a, dim3 grid, size_t smem, cudaStream_t s)
 {
-    CU_TRY(cudaFuncSetAttribute(me::nlm_kernel<TWS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int rc = raise_smem_limit((const void *)me::nlm_kernel<TWS>, false);
+    if (rc) return rc;
     me::nlm_kernel<TWS><<<grid, me::kNlmThreads, smem, s>>>(a);
     CU_TRY(cudaGetLastError());
     return ME_OK;
@@ -621,6 +644,9 @@ int me_create(int device, int height, int width, const me_params *params, int ma
     CREATE_TRY(cudaEventCreate(&c->ev_k1));
     CREATE_TRY(cudaEventCreate(&c->ev_t0));
     CREATE_TRY(cudaEventCreate(&c->ev_t1));
+    CREATE_TRY(cudaEventCreate(&c->ev_c0));
+    CREATE_TRY(cudaEventCreate(&c->ev_c1));
+    CREATE_TRY(cudaEventCreateWithFlags(&c->ev_rec, cudaEventDisableTiming));
     for (auto &r : c->recent) CREATE_TRY(cudaEventCreateWithFlags(&r.done, cudaEventDisableTiming));
     // staging: two buffers, each >= one BGR frame and about 32 MiB for long uploads
     size_t want = (size_t)width * height * 3;
@@ -633,7 +659,7 @@ int me_create(int device, int height, int width, const me_params *params, int ma
         CREATE_TRY(cudaEventCreateWithFlags(&c->stage_free[i], cudaEventDisableTiming));
     }
     CREATE_TRY(cudaHostAlloc(&c->h_pairs, sizeof(int32_t) * 2 * (size_t)max_pairs, cudaHostAllocDefault));
-    CREATE_TRY(cudaHostAlloc(&c->h_pair_out, sizeof(me_pair_result) * (size_t)max_pairs, cudaHostAllocDefault));
+    CREATE_TRY(cudaHostAlloc(&c->h_pair_out, sizeof(me_pair_result) * ((size_t)max_pairs + 1), cudaHostAllocDefault));   // + the error word of the scan
     CREATE_TRY(cudaMalloc(&c->d_pairs, sizeof(int32_t) * 2 * (size_t)max_pairs));
     const size_t nb = (size_t)c->args.nb * (size_t)max_pairs;
     CREATE_TRY(cudaMalloc(&c->args.blk_mv, nb * 2 * sizeof(int16_t)));
@@ -650,26 +676,15 @@ int me_create(int device, int height, int width, const me_params *params, int ma
         CREATE_TRY(cudaMemset(c->args.blk_key, 0xff, nb * sizeof(unsigned long long)));
         CREATE_TRY(cudaMalloc(&c->args.tile_ticket, nt * sizeof(unsigned)));
         CREATE_TRY(cudaMemset(c->args.tile_ticket, 0, nt * sizeof(unsigned)));
+        c->n_tile_tickets = nt;
     }
     CREATE_TRY(cudaMalloc(&c->d_ready, sizeof(int) * (size_t)(max_pairs + 2)));
     CREATE_TRY(cudaMalloc(&c->d_error, sizeof(int)));
     CREATE_TRY(cudaMemset(c->d_error, 0, sizeof(int)));
-    if (c->smem_persistent) {
-        CREATE_TRY(cudaFuncSetAttribute(c->kc.fn_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, c->smem_persistent));
-        CREATE_TRY(cudaFuncSetAttribute(c->kc.fn_persistent, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    }
-    CREATE_TRY(cudaFuncSetAttribute(c->kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, c->smem));
-    CREATE_TRY(cudaFuncSetAttribute(c->kc.fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     if (me_ctx *b = c->big) {                            // same outputs and scratch, its own kernels and launch shape
         b->args.blk_mv = c->args.blk_mv; b->args.blk_sad = c->args.blk_sad; b->args.blk_sub = c->args.blk_sub;
         b->args.blk_flags = c->args.blk_flags; b->args.pair_out = c->args.pair_out; b->args.pair_ticket = c->args.pair_ticket;
         b->args.blk_key = c->args.blk_key; b->args.tile_ticket = c->args.tile_ticket;
-        if (b->smem_persistent) {
-            CREATE_TRY(cudaFuncSetAttribute(b->kc.fn_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, b->smem_persistent));
-            CREATE_TRY(cudaFuncSetAttribute(b->kc.fn_persistent, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-        }
-        CREATE_TRY(cudaFuncSetAttribute(b->kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, b->smem));
-        CREATE_TRY(cudaFuncSetAttribute(b->kc.fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     }
 #undef CREATE_TRY
     rc = make_tensor_map(&c->tm_win, c->d_frames, c->W, c->H, max_frames, c->pitch, c->win_pitch, c->args.box_rows);
@@ -677,6 +692,11 @@ int me_create(int device, int height, int width, const me_params *params, int ma
     if (!rc && c->big) {
         rc = make_tensor_map(&c->big->tm_win, c->d_frames, c->W, c->H, max_frames, c->pitch, c->big->win_pitch, c->big->args.box_rows);
         if (!rc) rc = make_tensor_map(&c->big->tm_ref, c->d_frames, c->W, c->H, max_frames, c->pitch, me::kRefPitch, B * c->big->args.tmr);
+    }
+    for (const me_ctx *pl : {static_cast<const me_ctx *>(c), static_cast<const me_ctx *>(c->big)}) {
+        if (!pl || rc) continue;
+        rc = raise_smem_limit(pl->kc.fn);
+        if (!rc && pl->smem_persistent) rc = raise_smem_limit(pl->kc.fn_persistent);
     }
     if (rc) { me_destroy(c); return rc; }
     *out = c;
@@ -707,6 +727,9 @@ int me_destroy(me_ctx *c)
     if (c->ev_k1) cudaEventDestroy(c->ev_k1);
     if (c->ev_t0) cudaEventDestroy(c->ev_t0);
     if (c->ev_t1) cudaEventDestroy(c->ev_t1);
+    if (c->ev_c0) cudaEventDestroy(c->ev_c0);
+    if (c->ev_c1) cudaEventDestroy(c->ev_c1);
+    if (c->ev_rec) cudaEventDestroy(c->ev_rec);
     for (auto &r : c->recent) if (r.done) cudaEventDestroy(r.done);
     if (c->s_copy) cudaStreamDestroy(c->s_copy);
     if (c->s_compute) cudaStreamDestroy(c->s_compute);
@@ -891,6 +914,20 @@ int me_download(me_ctx *c, uint8_t *luma, size_t row_pitch, int first_slot, int 
     return ME_OK;
 }
 
+int me_copy_frames_device(me_ctx *c, void *d_dst, size_t dst_pitch, int first_slot, int n_frames, void *stream)
+{
+    if (!c || !d_dst) return fail(ME_EINVAL, "NULL argument");
+    if (n_frames < 1 || first_slot < 0 || first_slot + n_frames > c->max_frames)
+        return fail(ME_EINVAL, "%d frames at slot %d do not fit the %d-slot ring", n_frames, first_slot, c->max_frames);
+    if (dst_pitch < (size_t)c->W) return fail(ME_EINVAL, "dst_pitch %zu < width %d", dst_pitch, c->W);
+    CU_TRY(cudaSetDevice(c->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : c->s_copy;
+    if (st != c->s_copy && c->have_upload) CU_TRY(cudaStreamWaitEvent(st, c->ev_upload, 0));
+    CU_TRY(cudaMemcpy2DAsync(d_dst, dst_pitch, c->d_frames + (size_t)first_slot * c->frame_stride, c->pitch, (size_t)c->W,
+                             (size_t)n_frames * c->H, cudaMemcpyDeviceToDevice, st));
+    return ME_OK;
+}
+
 int me_search(me_ctx *c, const int32_t *pairs, int n_pairs)
 {
     if (!c) return fail(ME_EINVAL, "ctx is NULL");
@@ -956,7 +993,7 @@ int me_fetch_pairs(me_ctx *c, me_pair_result *out, int n_pairs)
     int err = 0;
     CU_TRY(cudaMemcpyAsync(&err, c->d_error, sizeof(int), cudaMemcpyDeviceToHost, c->s_compute));
     CU_TRY(cudaStreamSynchronize(c->s_compute));
-    if (err) return fail(ME_ECUDA, "the resident search kernel gave up waiting for a frame pair to complete (internal error)");
+    if (err) return report_search_timeout(c);
     memcpy(out, c->h_pair_out, sizeof(me_pair_result) * (size_t)n_pairs);
     return ME_OK;
 }
@@ -973,7 +1010,10 @@ int me_fetch_blocks(me_ctx *c, int pair_index, int16_t *mv, uint32_t *sad, float
     if (sad) CU_TRY(cudaMemcpyAsync(sad, c->args.blk_sad + o, nb * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     if (sub) CU_TRY(cudaMemcpyAsync(sub, c->args.blk_sub + o * 2, nb * 2 * sizeof(float), cudaMemcpyDeviceToHost, st));
     if (flags) CU_TRY(cudaMemcpyAsync(flags, c->args.blk_flags + o, nb, cudaMemcpyDeviceToHost, st));
+    int err = 0;
+    CU_TRY(cudaMemcpyAsync(&err, c->d_error, sizeof(int), cudaMemcpyDeviceToHost, st));
     CU_TRY(cudaStreamSynchronize(st));
+    if (err) return report_search_timeout(c);
     return ME_OK;
 }
 
@@ -986,6 +1026,67 @@ int me_estimate_pair(me_ctx *c, const uint8_t *prev, const uint8_t *cur, size_t 
     if (!rc) rc = me_search(c, pr, 1);
     if (!rc) rc = me_fetch_pairs(c, out, 1);
     return rc;
+}
+
+int me_anchored_scan(me_ctx *c, int anchor_slot, int first_slot, int n_frames, float scale, float gate,
+                     me_scan_record *out, int *searches, int *launches)
+{
+    if (!c || !out) return fail(ME_EINVAL, "NULL argument");
+    if (n_frames < 1 || first_slot < 0 || first_slot + n_frames > c->max_frames || anchor_slot < 0 || anchor_slot >= c->max_frames)
+        return fail(ME_EINVAL, "scan of %d frames at slot %d with the anchor in slot %d does not fit the %d-slot ring", n_frames,
+                    first_slot, anchor_slot, c->max_frames);
+    CU_TRY(cudaSetDevice(c->device));
+    if (c->have_search) CU_TRY(cudaEventSynchronize(c->ev_search));   // h_pairs / h_pair_out are about to be reused
+    if (c->have_upload) CU_TRY(cudaStreamWaitEvent(c->s_compute, c->ev_upload, 0));
+    cudaStream_t st = c->s_compute;
+    int *h_err = reinterpret_cast<int *>(c->h_pair_out + c->max_pairs);
+    const int end = first_slot + n_frames, max_look = c->max_pairs < 256 ? c->max_pairs : 256;
+    int anchor = anchor_slot, k = first_slot, look = max_look < 4 ? max_look : 4, since = 0, n_search = 0, n_launch = 0, last = 0;
+    int lo = anchor_slot < first_slot ? anchor_slot : first_slot, hi = anchor_slot > end - 1 ? anchor_slot : end - 1;
+    while (k < end) {
+        const int L = std::min(std::min(look, end - k), c->max_pairs);
+        for (int i = 0; i < L; ++i) { c->h_pairs[2 * i] = anchor; c->h_pairs[2 * i + 1] = k + i; }
+        CU_TRY(cudaMemcpyAsync(c->d_pairs, c->h_pairs, sizeof(int32_t) * 2 * (size_t)L, cudaMemcpyHostToDevice, st));
+        const me_ctx *pl = pick_plan(c, L);
+        int rc = launch_search(c, pl, c->d_frames, pl->tm_win, pl->tm_ref, L, st);
+        if (rc) return rc;
+        CU_TRY(cudaMemcpyAsync(c->h_pair_out, c->args.pair_out, sizeof(me_pair_result) * (size_t)L, cudaMemcpyDeviceToHost, st));
+        CU_TRY(cudaMemcpyAsync(h_err, c->d_error, sizeof(int), cudaMemcpyDeviceToHost, st));
+        CU_TRY(cudaStreamSynchronize(st));
+        c->have_search = true;
+        c->last_pairs = last = L;
+        if (*h_err) return report_search_timeout(c);
+        ++n_launch;
+        n_search += L;
+        int acc = -1;
+        for (int i = 0; i < L; ++i) {
+            const me_pair_result &r = c->h_pair_out[i];
+            const bool skip = (r.pdx * scale < gate) && r.flag == 1;          // estimate_vel_vid.py:531-534
+            me_scan_record &o = out[k + i - first_slot];
+            o.anchor_slot = anchor; o.accepted = skip ? 0 : 1; o.pair = r;
+            if (!skip) { acc = i; break; }                                     // :575 -- the rest of the batch compared with a stale anchor
+        }
+        if (acc >= 0) {
+            const int dist = since + acc + 1;                                  // frames from the old anchor to the new one
+            anchor = k + acc; k += acc + 1; since = 0;
+            look = std::min(std::max(dist + 1, 2), max_look);                  // expect the next accept about as far away
+        } else {
+            since += L; k += L;
+            look = std::min(2 * look, max_look);                               // same anchor: look further
+        }
+    }
+    CU_TRY(cudaEventRecord(c->ev_search, st));
+    {
+        me_ctx::SearchRecord &r = c->recent[c->recent_next];
+        c->recent_next = (c->recent_next + 1) % 4;
+        r.lo = lo; r.hi = hi;
+        CU_TRY(cudaEventRecord(r.done, st));
+        r.used = true;
+    }
+    (void)last;
+    if (searches) *searches = n_search;
+    if (launches) *launches = n_launch;
+    return ME_OK;
 }
 
 int me_sync(me_ctx *c)
@@ -1024,6 +1125,40 @@ int me_timer_stop(me_ctx *c, float *ms)
     CU_TRY(cudaEventRecord(c->ev_t1, c->s_compute));
     CU_TRY(cudaEventSynchronize(c->ev_t1));
     CU_TRY(cudaEventElapsedTime(ms, c->ev_t0, c->ev_t1));
+    return ME_OK;
+}
+
+int me_copy_timer_start(me_ctx *c)
+{
+    if (!c) return fail(ME_EINVAL, "ctx is NULL");
+    CU_TRY(cudaSetDevice(c->device));
+    CU_TRY(cudaEventRecord(c->ev_c0, c->s_copy));
+    return ME_OK;
+}
+
+int me_copy_timer_stop(me_ctx *c, float *ms)
+{
+    if (!c || !ms) return fail(ME_EINVAL, "NULL argument");
+    CU_TRY(cudaSetDevice(c->device));
+    CU_TRY(cudaEventRecord(c->ev_c1, c->s_copy));
+    CU_TRY(cudaEventSynchronize(c->ev_c1));
+    CU_TRY(cudaEventElapsedTime(ms, c->ev_c0, c->ev_c1));
+    return ME_OK;
+}
+
+int me_copy_pair_records_device(me_ctx *c, void *d_dst, int n_pairs, void *stream)
+{
+    if (!c || !d_dst) return fail(ME_EINVAL, "NULL argument");
+    if (!c->have_search) return fail(ME_ESTATE, "me_copy_pair_records_device before any me_search");
+    if (n_pairs < 1 || n_pairs > c->last_pairs) return fail(ME_EINVAL, "n_pairs=%d, last search had %d", n_pairs, c->last_pairs);
+    CU_TRY(cudaSetDevice(c->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : c->s_compute;
+    if (st != c->s_compute) CU_TRY(cudaStreamWaitEvent(st, c->ev_search, 0));
+    CU_TRY(cudaMemcpyAsync(d_dst, c->args.pair_out, sizeof(me_pair_result) * (size_t)n_pairs, cudaMemcpyDeviceToDevice, st));
+    if (st != c->s_compute) {                        // later searches on the compute stream wait for this copy (launch_search)
+        CU_TRY(cudaEventRecord(c->ev_rec, st));
+        c->have_rec = true;
+    }
     return ME_OK;
 }
 
@@ -1097,6 +1232,9 @@ static __device__ __align__(256) unsigned char g_static_scratch[ME_STATIC_SCRATC
 namespace {
 
 struct StaticDevice {
+    std::once_flag once;                // two host threads may make their first call on a device together
+    int rc = ME_OK;
+    char err[256] = "";
     bool ready = false;
     unsigned char *scratch = nullptr;   // device address of g_static_scratch on this device
     int sm_count = 0;
@@ -1110,14 +1248,20 @@ inline size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
 int static_device_setup(int dev)
 {
     StaticDevice &d = g_static_dev[dev];
-    if (d.ready) return ME_OK;
-    void *ptr = nullptr;
-    CU_TRY(cudaGetSymbolAddress(&ptr, g_static_scratch));
-    if (!ptr) return fail(ME_ECUDA, "cudaGetSymbolAddress returned a null address for the static scratch array");
-    CU_TRY(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, dev));
-    d.scratch = static_cast<unsigned char *>(ptr);
-    d.ready = true;
-    return ME_OK;
+    std::call_once(d.once, [&d, dev]() {
+        void *ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_scratch);
+        if (e == cudaSuccess && !ptr) e = cudaErrorInvalidSymbol;
+        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, dev);
+        if (e != cudaSuccess) {
+            d.rc = ME_ECUDA;
+            snprintf(d.err, sizeof d.err, "static scratch set-up on device %d failed: %s", dev, cudaGetErrorString(e));
+            return;
+        }
+        d.scratch = static_cast<unsigned char *>(ptr);
+        d.ready = true;
+    });
+    return d.ready ? ME_OK : fail(d.rc ? d.rc : ME_ECUDA, "%s", d.err);
 }
 
 } // namespace
@@ -1177,8 +1321,8 @@ extern "C" int me_search_static_scratch(const uint8_t *d_frames, size_t pitch, i
     rc = make_tensor_map(&tw, d_frames, width, height, n_frames, pitch, plan.win_pitch, plan.args.box_rows);
     if (!rc) rc = make_tensor_map(&tr, d_frames, width, height, n_frames, pitch, me::kRefPitch, B * plan.args.tmr);
     if (rc) return rc;
-    CU_TRY(cudaFuncSetAttribute(plan.kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, plan.smem));
-    CU_TRY(cudaFuncSetAttribute(plan.kc.fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    rc = raise_smem_limit(plan.kc.fn);
+    if (rc) return rc;
 
     me::SearchArgs a = plan.args;
     a.frames = d_frames;

@@ -289,62 +289,8 @@ sad_search_persistent(const __grid_constant__ CUtensorMap tm_win, const __grid_c
                 }
                 mbar_wait(&bars[s], full_phase[s] & 1);
                 ++full_phase[s];
-                // byte-shifted copies (same arithmetic as sad_search_kernel), one warp
-                const int chunks = a.n_row_boxes * a.box_rows * (PITCH >> 4);
-                const uint32_t *raw = reinterpret_cast<const uint32_t *>(s_raw);
-                if (a.x_off == 0) {
-                    for (int i = warp * 32 + lane; i < chunks; i += 32 * NP) {
-                        const uint4 v = *reinterpret_cast<const uint4 *>(raw + 4 * i);
-                        const uint32_t w4 = raw[4 * i + 4];
-#pragma unroll
-                        for (int sft = 1; sft < 4; ++sft) {
-                            uint4 o;
-                            o.x = __funnelshift_r(v.x, v.y, 8 * sft);
-                            o.y = __funnelshift_r(v.y, v.z, 8 * sft);
-                            o.z = __funnelshift_r(v.z, v.w, 8 * sft);
-                            o.w = __funnelshift_r(v.w, w4, 8 * sft);
-                            *reinterpret_cast<uint4 *>(s_win + (size_t)sft * (a.copy_bytes + kCopySkew) + 16 * (size_t)i) = o;
-                        }
-                    }
-                } else if ((a.x_off & 3) == 0) {                          // see sad_search_kernel: whole-word offset, no selects
-                    const uint32_t *rawo = raw + (a.x_off >> 2);
-                    for (int i = warp * 32 + lane; i < chunks; i += 32 * NP) {
-                        const uint32_t e0 = rawo[4 * i], e1 = rawo[4 * i + 1], e2 = rawo[4 * i + 2], e3 = rawo[4 * i + 3], e4 = rawo[4 * i + 4];
-                        *reinterpret_cast<uint4 *>(s_win + 16 * (size_t)i) = make_uint4(e0, e1, e2, e3);
-#pragma unroll
-                        for (int sft = 1; sft < 4; ++sft) {
-                            uint4 o;
-                            o.x = __funnelshift_r(e0, e1, 8 * sft);
-                            o.y = __funnelshift_r(e1, e2, 8 * sft);
-                            o.z = __funnelshift_r(e2, e3, 8 * sft);
-                            o.w = __funnelshift_r(e3, e4, 8 * sft);
-                            *reinterpret_cast<uint4 *>(s_win + (size_t)sft * (a.copy_bytes + kCopySkew) + 16 * (size_t)i) = o;
-                        }
-                    }
-                } else {
-                    for (int i = warp * 32 + lane; i < chunks; i += 32 * NP) {
-                        uint32_t w[9];
-                        const uint4 v0 = *reinterpret_cast<const uint4 *>(raw + 4 * i);
-                        const uint4 v1 = *reinterpret_cast<const uint4 *>(raw + 4 * i + 4);
-                        w[0] = v0.x; w[1] = v0.y; w[2] = v0.z; w[3] = v0.w; w[4] = v1.x; w[5] = v1.y; w[6] = v1.z; w[7] = v1.w;
-                        w[8] = raw[4 * i + 8];
-#pragma unroll
-                        for (int sft = 0; sft < 4; ++sft) {
-                            const int sh = a.x_off + sft, wo = sh >> 2;
-                            const unsigned bits = (unsigned)(sh & 3) * 8;
-                            uint32_t e[5];
-#pragma unroll
-                            for (int q = 0; q < 5; ++q)
-                                e[q] = wo == 0 ? w[q] : wo == 1 ? w[q + 1] : wo == 2 ? w[q + 2] : wo == 3 ? w[q + 3] : w[q + 4];
-                            uint4 o;
-                            o.x = __funnelshift_r(e[0], e[1], bits);
-                            o.y = __funnelshift_r(e[1], e[2], bits);
-                            o.z = __funnelshift_r(e[2], e[3], bits);
-                            o.w = __funnelshift_r(e[3], e[4], bits);
-                            *reinterpret_cast<uint4 *>(s_win + (size_t)sft * (a.copy_bytes + kCopySkew) + 16 * (size_t)i) = o;
-                        }
-                    }
-                }
+                // byte-shifted copies: chunk i goes to producer thread i mod (32 * NP)
+                build_shifted_copies<PITCH>(a, s_raw, s_win, warp * 32 + lane, 32 * NP);
             }
             __threadfence_block();
             __syncwarp();

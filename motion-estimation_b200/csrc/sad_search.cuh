@@ -225,6 +225,72 @@ __device__ __forceinline__ void sad_patch(const uint32_t *__restrict__ cur, cons
     }
 }
 
+// ---------------------------------------------------------------- shifted window copies
+// Derive the four byte-shifted copies of a staged window: copy s, byte k of a row = raw byte (x_off + s + k).
+// Threads first, first + step, ... of the calling group take one 16-byte chunk each per round (the whole CTA in
+// sad_search_kernel, the producer warps in sad_search_persistent).
+template <int PITCH>
+__device__ __forceinline__ void build_shifted_copies(const SearchArgs &a, const uint8_t *s_raw, uint8_t *s_win, int first, int step)
+{
+    const int chunks = a.n_row_boxes * a.box_rows * (PITCH >> 4);   // 16-byte chunks per copy
+    const uint32_t *raw = reinterpret_cast<const uint32_t *>(s_raw);
+    if (a.x_off == 0) {                                             // copy 0 is the TMA destination itself
+        for (int i = first; i < chunks; i += step) {
+            const uint4 v = *reinterpret_cast<const uint4 *>(raw + 4 * i);
+            const uint32_t w4 = raw[4 * i + 4];                     // next chunk's first word (slack at the very end)
+#pragma unroll
+            for (int s = 1; s < 4; ++s) {
+                uint4 o;
+                o.x = __funnelshift_r(v.x, v.y, 8 * s);
+                o.y = __funnelshift_r(v.y, v.z, 8 * s);
+                o.z = __funnelshift_r(v.z, v.w, 8 * s);
+                o.w = __funnelshift_r(v.w, w4, 8 * s);
+                *reinterpret_cast<uint4 *>(s_win + (size_t)s * (a.copy_bytes + kCopySkew) + 16 * (size_t)i) = o;
+            }
+        }
+    } else if ((a.x_off & 3) == 0) {
+        // window origin a whole number of words off the aligned one (even ranges: +-8, +-24, +-40): copy s is the raw
+        // row from word x_off/4 on, funnel-shifted by s bytes -- no per-word selects
+        const uint32_t *rawo = raw + (a.x_off >> 2);
+        for (int i = first; i < chunks; i += step) {
+            const uint32_t e0 = rawo[4 * i], e1 = rawo[4 * i + 1], e2 = rawo[4 * i + 2], e3 = rawo[4 * i + 3], e4 = rawo[4 * i + 4];
+            *reinterpret_cast<uint4 *>(s_win + 16 * (size_t)i) = make_uint4(e0, e1, e2, e3);
+#pragma unroll
+            for (int s = 1; s < 4; ++s) {
+                uint4 o;
+                o.x = __funnelshift_r(e0, e1, 8 * s);
+                o.y = __funnelshift_r(e1, e2, 8 * s);
+                o.z = __funnelshift_r(e2, e3, 8 * s);
+                o.w = __funnelshift_r(e3, e4, 8 * s);
+                *reinterpret_cast<uint4 *>(s_win + (size_t)s * (a.copy_bytes + kCopySkew) + 16 * (size_t)i) = o;
+            }
+        }
+    } else {
+        for (int i = first; i < chunks; i += step) {
+            uint32_t w[9];
+            const uint4 v0 = *reinterpret_cast<const uint4 *>(raw + 4 * i);
+            const uint4 v1 = *reinterpret_cast<const uint4 *>(raw + 4 * i + 4);   // may run into the slack: unused bytes only
+            w[0] = v0.x; w[1] = v0.y; w[2] = v0.z; w[3] = v0.w; w[4] = v1.x; w[5] = v1.y; w[6] = v1.z; w[7] = v1.w;
+            w[8] = raw[4 * i + 8];
+#pragma unroll
+            for (int s = 0; s < 4; ++s) {
+                const int sh = a.x_off + s, wo = sh >> 2;
+                const unsigned bits = (unsigned)(sh & 3) * 8;
+                uint32_t e[5];                  // wo is 0..4: select statically to keep w[] in registers
+#pragma unroll
+                for (int k = 0; k < 5; ++k)
+                    e[k] = wo == 0 ? w[k] : wo == 1 ? w[k + 1] : wo == 2 ? w[k + 2] : wo == 3 ? w[k + 3] : w[k + 4];
+                uint4 o;
+                o.x = __funnelshift_r(e[0], e[1], bits);
+                o.y = __funnelshift_r(e[1], e[2], bits);
+                o.z = __funnelshift_r(e[2], e[3], bits);
+                o.w = __funnelshift_r(e[3], e[4], bits);
+                *reinterpret_cast<uint4 *>(s_win + (size_t)s * (a.copy_bytes + kCopySkew) + 16 * (size_t)i) = o;
+            }
+        }
+    }
+}
+
 // ---------------------------------------------------------------- finalize helpers
 // 4 bytes from an arbitrary byte address, using aligned word loads only.  The second word is
 // touched only when it holds a needed byte, so an in-frame request never leaves its row pitch.
@@ -385,19 +451,20 @@ constexpr uint32_t kNoKey = 0u;        // fkey() of a finite float is never 0
 constexpr int kSelBins = 2048;         // 11 bits per level; 2 axes x 2048 x 4 B = 16 KB of the CTA's shared memory
 constexpr int kSelUnroll = 8;
 
-__device__ __forceinline__ void pair_keys(const uint8_t *fl, const float2 *sub, int b, uint32_t &kx, uint32_t &ky)
+__device__ __forceinline__ void pair_keys(const uint8_t *fl, const float2 *sub, int b, uint32_t &kx, uint32_t &ky, unsigned &tex, float2 &v)
 {
     const unsigned f = __ldcg(fl + b);
-    const float2 v = __ldcg(sub + b);
+    tex = f & ME_FLAG_TEXTURED;
+    v = __ldcg(sub + b);
     kx = (f & (ME_FLAG_TEXTURED | ME_FLAG_X_PEAKED)) == (ME_FLAG_TEXTURED | ME_FLAG_X_PEAKED) ? fkey(v.x) : kNoKey;
     ky = (f & (ME_FLAG_TEXTURED | ME_FLAG_Y_PEAKED)) == (ME_FLAG_TEXTURED | ME_FLAG_Y_PEAKED) ? fkey(v.y) : kNoKey;
 }
 
 // scratch: the CTA's shared memory from offset 0 (at least 2*kSelBins*4 + 128 bytes)
-__device__ void reduce_pair(const SearchArgs &a, int pair, unsigned *scratch)
+static __device__ void reduce_pair(const SearchArgs &a, int pair, unsigned *scratch)
 {
     unsigned *hist = scratch;                    // [2][kSelBins]
-    unsigned *bc = scratch + 2 * kSelBins;       // per axis: [0] chosen bin, [1] rank inside it, [2] its count, [3] total
+    unsigned *bc = scratch + 2 * kSelBins;       // per axis: [0] chosen bin, [1] rank inside it, [2] its count, [3] total; [8],[9] next keys; [10] textured; [12..15] field sums
     const uint8_t *fl = a.blk_flags + (size_t)pair * a.nb;
     const float2 *sub = reinterpret_cast<const float2 *>(a.blk_sub) + (size_t)pair * a.nb;
     const int T = blockDim.x, tid = threadIdx.x;
@@ -408,18 +475,41 @@ __device__ void reduce_pair(const SearchArgs &a, int pair, unsigned *scratch)
         const int shift = level == 0 ? 21 : level == 1 ? 10 : 0;
         const uint32_t bmask = level == 2 ? 1023u : 2047u;
         for (int i = tid; i < 2 * kSelBins; i += T) hist[i] = 0;
+        if (level == 0 && tid < 6) bc[10 + tid] = 0;          // [10] textured count, [12..15] the two 64-bit field sums
         __syncthreads();
+        unsigned ntex = 0;
+        long long fsx = 0, fsy = 0;                  // spec "mean": exact 2^-20 fixed-point sums of the valid displacements
         for (int b0 = tid; b0 < a.nb; b0 += kSelUnroll * T) {
             uint32_t kx[kSelUnroll], ky[kSelUnroll];
 #pragma unroll
             for (int u = 0; u < kSelUnroll; ++u) {
                 kx[u] = ky[u] = kNoKey;
-                if (b0 + u * T < a.nb) pair_keys(fl, sub, b0 + u * T, kx[u], ky[u]);
+                unsigned tex = 0;
+                float2 v = make_float2(0.f, 0.f);
+                if (b0 + u * T < a.nb) pair_keys(fl, sub, b0 + u * T, kx[u], ky[u], tex, v);
+                ntex += tex;
+                if (level == 0) {
+                    if (kx[u] != kNoKey) fsx += (long long)__float2ll_rn(__fmul_rn(v.x, 1048576.0f));
+                    if (ky[u] != kNoKey) fsy += (long long)__float2ll_rn(__fmul_rn(v.y, 1048576.0f));
+                }
             }
 #pragma unroll
             for (int u = 0; u < kSelUnroll; ++u) {
                 if (kx[u] != kNoKey && (kx[u] & mask[0]) == prefix[0]) atomicAdd(&hist[(kx[u] >> shift) & bmask], 1u);
                 if (ky[u] != kNoKey && (ky[u] & mask[1]) == prefix[1]) atomicAdd(&hist[kSelBins + ((ky[u] >> shift) & bmask)], 1u);
+            }
+        }
+        if (level == 0) {                            // the first pass also counts the textured blocks and sums the field
+            ntex = __reduce_add_sync(kFull, ntex);
+#pragma unroll
+            for (int o = 16; o; o >>= 1) {
+                fsx += __shfl_xor_sync(kFull, fsx, o);
+                fsy += __shfl_xor_sync(kFull, fsy, o);
+            }
+            if ((tid & 31) == 0) {
+                if (ntex) atomicAdd(&bc[10], ntex);
+                if (fsx) atomicAdd(reinterpret_cast<unsigned long long *>(bc + 12), (unsigned long long)fsx);
+                if (fsy) atomicAdd(reinterpret_cast<unsigned long long *>(bc + 14), (unsigned long long)fsy);
             }
         }
         __syncthreads();
@@ -476,7 +566,9 @@ __device__ void reduce_pair(const SearchArgs &a, int pair, unsigned *scratch)
 #pragma unroll
             for (int u = 0; u < kSelUnroll; ++u) {
                 kx[u] = ky[u] = kNoKey;
-                if (b0 + u * T < a.nb) pair_keys(fl, sub, b0 + u * T, kx[u], ky[u]);
+                unsigned tex;
+                float2 v;
+                if (b0 + u * T < a.nb) pair_keys(fl, sub, b0 + u * T, kx[u], ky[u], tex, v);
             }
 #pragma unroll
             for (int u = 0; u < kSelUnroll; ++u) {
@@ -498,7 +590,10 @@ __device__ void reduce_pair(const SearchArgs &a, int pair, unsigned *scratch)
         r.flag = (int)cnt[0] >= (a.min_valid > 1 ? a.min_valid : 1);
         r.nvalid_x = (int)cnt[0];
         r.nvalid_y = (int)cnt[1];
-        r.reserved = 0;
+        r.n_textured = (int)bc[10];
+        const long long sx = *reinterpret_cast<const long long *>(bc + 12), sy = *reinterpret_cast<const long long *>(bc + 14);
+        r.mean_dx = cnt[0] ? (float)__ddiv_rn((double)sx, __dmul_rn((double)cnt[0], 1048576.0)) : 0.0f;
+        r.mean_dy = cnt[1] ? (float)__ddiv_rn((double)sy, __dmul_rn((double)cnt[1], 1048576.0)) : 0.0f;
         a.pair_out[pair] = r;
         a.pair_ticket[pair] = 0;                    // leave the scratch clean for the next launch
     }
@@ -658,7 +753,7 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     // block rows at the top and bottom of the frame (all rows of the 64-pixel-tall recordings).
     const int dy_cap = max(dyi_hi - NDY + 1, 0);
     const int nd = dyi_hi >= dyi_lo ? (dyi_hi - dyi_lo) / NDY + 1 : 0; // 0: this slab holds no candidate of this block row
-    if (tid < kMaxTileKeys) s_key[tid] = kNone;
+    for (int i = tid; i < kMaxTileKeys; i += (int)blockDim.x) s_key[i] = kNone;
 
     const int wx0 = X0 - a.R - a.x_off + ubase, wy0 = Y0 - a.R + dbase;   // wx0 is a multiple of 16 (su is)
     if (nd == 0) {
@@ -695,65 +790,9 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
         __syncthreads();
     }
 
-    // ---- derive the byte-shifted copies: copy s, byte k of a row = raw byte (x_off + s + k)
+    // ---- derive the byte-shifted copies
     if (nd > 0) {
-        const int chunks = a.n_row_boxes * a.box_rows * (PITCH >> 4);   // 16-byte chunks per copy
-        const uint32_t *raw = reinterpret_cast<const uint32_t *>(s_raw);
-        if (a.x_off == 0) {                                             // copy 0 is the TMA destination itself
-            for (int i = tid; i < chunks; i += blockDim.x) {
-                const uint4 v = *reinterpret_cast<const uint4 *>(raw + 4 * i);
-                const uint32_t w4 = raw[4 * i + 4];                     // next chunk's first word (slack at the very end)
-#pragma unroll
-                for (int s = 1; s < 4; ++s) {
-                    uint4 o;
-                    o.x = __funnelshift_r(v.x, v.y, 8 * s);
-                    o.y = __funnelshift_r(v.y, v.z, 8 * s);
-                    o.z = __funnelshift_r(v.z, v.w, 8 * s);
-                    o.w = __funnelshift_r(v.w, w4, 8 * s);
-                    *reinterpret_cast<uint4 *>(s_win + (size_t)s * (a.copy_bytes + kCopySkew) + 16 * (size_t)i) = o;
-                }
-            }
-        } else if ((a.x_off & 3) == 0) {
-            // window origin a whole number of words off the aligned one (even ranges: +-8, +-24, +-40): copy s is the raw
-            // row from word x_off/4 on, funnel-shifted by s bytes -- no per-word selects
-            const uint32_t *rawo = raw + (a.x_off >> 2);
-            for (int i = tid; i < chunks; i += blockDim.x) {
-                const uint32_t e0 = rawo[4 * i], e1 = rawo[4 * i + 1], e2 = rawo[4 * i + 2], e3 = rawo[4 * i + 3], e4 = rawo[4 * i + 4];
-                *reinterpret_cast<uint4 *>(s_win + 16 * (size_t)i) = make_uint4(e0, e1, e2, e3);
-#pragma unroll
-                for (int s = 1; s < 4; ++s) {
-                    uint4 o;
-                    o.x = __funnelshift_r(e0, e1, 8 * s);
-                    o.y = __funnelshift_r(e1, e2, 8 * s);
-                    o.z = __funnelshift_r(e2, e3, 8 * s);
-                    o.w = __funnelshift_r(e3, e4, 8 * s);
-                    *reinterpret_cast<uint4 *>(s_win + (size_t)s * (a.copy_bytes + kCopySkew) + 16 * (size_t)i) = o;
-                }
-            }
-        } else {
-            for (int i = tid; i < chunks; i += blockDim.x) {
-                uint32_t w[9];
-                const uint4 v0 = *reinterpret_cast<const uint4 *>(raw + 4 * i);
-                const uint4 v1 = *reinterpret_cast<const uint4 *>(raw + 4 * i + 4);   // may run into the slack: unused bytes only
-                w[0] = v0.x; w[1] = v0.y; w[2] = v0.z; w[3] = v0.w; w[4] = v1.x; w[5] = v1.y; w[6] = v1.z; w[7] = v1.w;
-                w[8] = raw[4 * i + 8];
-#pragma unroll
-                for (int s = 0; s < 4; ++s) {
-                    const int sh = a.x_off + s, wo = sh >> 2;
-                    const unsigned bits = (unsigned)(sh & 3) * 8;
-                    uint32_t e[5];                  // wo is 0..4: select statically to keep w[] in registers
-#pragma unroll
-                    for (int k = 0; k < 5; ++k)
-                        e[k] = wo == 0 ? w[k] : wo == 1 ? w[k + 1] : wo == 2 ? w[k + 2] : wo == 3 ? w[k + 3] : w[k + 4];
-                    uint4 o;
-                    o.x = __funnelshift_r(e[0], e[1], bits);
-                    o.y = __funnelshift_r(e[1], e[2], bits);
-                    o.z = __funnelshift_r(e[2], e[3], bits);
-                    o.w = __funnelshift_r(e[3], e[4], bits);
-                    *reinterpret_cast<uint4 *>(s_win + (size_t)s * (a.copy_bytes + kCopySkew) + 16 * (size_t)i) = o;
-                }
-            }
-        }
+        build_shifted_copies<PITCH>(a, s_raw, s_win, tid, (int)blockDim.x);
         __syncthreads();
     }
 
@@ -882,57 +921,6 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
         __threadfence();
         reduce_pair(a, pair, reinterpret_cast<unsigned *>(smem));
     }
-}
-
-// ---------------------------------------------------------------- BGR -> luma (ingest, a9)
-// cv.cvtColor(BGR2GRAY) for 8-bit: Y = (B*3735 + G*19235 + R*9798 + 16384) >> 15 (cv2 4.13, checked in tests).
-__global__ void bgr2gray_kernel(const uint8_t *__restrict__ bgr, size_t bgr_pitch, uint8_t *__restrict__ gray,
-                                size_t gray_pitch, int W, int rows)
-{
-    const int x4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
-    const int y = blockIdx.y;
-    if (x4 >= W || y >= rows) return;
-    const uint8_t *p = bgr + (size_t)y * bgr_pitch + (size_t)x4 * 3;
-    uint8_t o[4] = {0, 0, 0, 0};
-    const int n = min(4, W - x4);
-    for (int i = 0; i < n; ++i)
-        o[i] = (uint8_t)((p[3 * i] * 3735u + p[3 * i + 1] * 19235u + p[3 * i + 2] * 9798u + 16384u) >> 15);
-    uint8_t *g = gray + (size_t)y * gray_pitch + x4;
-    if (n == 4) *reinterpret_cast<uchar4 *>(g) = make_uchar4(o[0], o[1], o[2], o[3]);
-    else for (int i = 0; i < n; ++i) g[i] = o[i];
-}
-
-// ---------------------------------------------------------------- issue-rate microbenchmark
-// Register-only 4x4 patch of VABSDIFF4.U8.ACC (the search kernel's operand pattern), one
-// 1024-thread CTA per SM.  MODE 1 adds one LDS.128 per 16 SAD ops (the kernel's load mix).
-template <int MODE>
-__global__ void __launch_bounds__(1024, 1) microbench_kernel(uint32_t *out, int iters, long long *clk, uint32_t seed)
-{
-    __shared__ uint4 sbuf[1024];
-    sbuf[threadIdx.x] = make_uint4(seed, seed * 3u, seed * 5u, seed * 7u);
-    __syncthreads();
-    uint32_t acc[16], a[4], b[4];
-#pragma unroll
-    for (int i = 0; i < 16; ++i) acc[i] = i;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) { a[i] = seed * (i + 1) + threadIdx.x; b[i] = seed ^ (i * 0x01010101u); }
-    const long long t0 = clock64();
-    for (int it = 0; it < iters; ++it) {
-#pragma unroll
-        for (int q = 0; q < 4; ++q)
-#pragma unroll
-            for (int d = 0; d < 4; ++d) acc[d * 4 + q] = vsad4(a[d], b[q], acc[d * 4 + q]);
-        if (MODE == 1) {
-            const uint4 v = sbuf[(threadIdx.x + it) & 1023];
-            b[0] ^= v.x; b[1] += v.y; b[2] ^= v.z; b[3] += v.w;
-        }
-    }
-    const long long t1 = clock64();
-    uint32_t s = 0;
-#pragma unroll
-    for (int i = 0; i < 16; ++i) s += acc[i];
-    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
-    if (threadIdx.x == 0) clk[blockIdx.x] = t1 - t0;
 }
 
 } // namespace me

@@ -16,7 +16,10 @@ from ._lib import Geometry, PairResult, Params, check
 FLAG_TEXTURED, FLAG_X_INTERIOR, FLAG_Y_INTERIOR, FLAG_X_PEAKED, FLAG_Y_PEAKED = 1, 2, 4, 8, 16
 
 PAIR_DTYPE = np.dtype([("pdx", "<f4"), ("pdy", "<f4"), ("flag", "<i4"), ("nvalid_x", "<i4"),
-                       ("nvalid_y", "<i4"), ("reserved", "<i4")])
+                       ("nvalid_y", "<i4"), ("n_textured", "<i4"), ("mean_dx", "<f4"), ("mean_dy", "<f4")])
+
+
+SCAN_DTYPE = np.dtype([("anchor_slot", "<i4"), ("accepted", "<i4"), ("pair", PAIR_DTYPE)])
 
 
 @dataclass(frozen=True)
@@ -143,6 +146,33 @@ class MotionEstimator:
                                        C.c_void_p(int(stream) if stream else None)))
         return p.shape[0]
 
+    def anchored_scan(self, anchor_slot, first_slot, n_frames, scale=0.5, gate=2.0):
+        """The video script's anchor walk (estimate_vel_vid.py:506-534, :575) over ring slots first_slot.. inside the library:
+        (records, searches, launches); records[i] describes slot first_slot + i (anchor slot, accepted, pair record)."""
+        out = np.zeros(int(n_frames), SCAN_DTYPE)
+        ns, nl = C.c_int(), C.c_int()
+        check(self._L.me_anchored_scan(self._ctx, int(anchor_slot), int(first_slot), int(n_frames), float(scale), float(gate),
+                                       out.ctypes.data, C.byref(ns), C.byref(nl)))
+        return out, ns.value, nl.value
+
+    def copy_pair_records_device(self, d_dst, n_pairs, stream=None):
+        """Records of the last search -> device memory at d_dst (e.g. a torch tensor's data_ptr()) on `stream`, no host bounce."""
+        check(self._L.me_copy_pair_records_device(self._ctx, C.c_void_p(int(d_dst)), int(n_pairs),
+                                                  C.c_void_p(int(stream) if stream else None)))
+
+    def copy_frames_device(self, d_dst, dst_pitch, first_slot, n_frames, stream=None):
+        """Ring slots -> device memory at d_dst (rows dst_pitch bytes apart), no host bounce."""
+        check(self._L.me_copy_frames_device(self._ctx, C.c_void_p(int(d_dst)), int(dst_pitch), int(first_slot), int(n_frames),
+                                            C.c_void_p(int(stream) if stream else None)))
+
+    def copy_timer_start(self):
+        check(self._L.me_copy_timer_start(self._ctx))
+
+    def copy_timer_stop(self) -> float:
+        ms = C.c_float()
+        check(self._L.me_copy_timer_stop(self._ctx, C.byref(ms)))
+        return float(ms.value)
+
     def fetch_blocks(self, pair_index=0):
         nb = (self.nby, self.nbx)
         mv = np.zeros(nb + (2,), np.int16)
@@ -162,7 +192,7 @@ class MotionEstimator:
         r = PairResult()
         check(self._L.me_estimate_pair(self._ctx, prev.ctypes.data, cur.ctypes.data, prev.strides[0], C.byref(r)))
         return dict(pdx=np.float32(r.pdx), pdy=np.float32(r.pdy), flag=int(r.flag), nvalid_x=int(r.nvalid_x),
-                    nvalid_y=int(r.nvalid_y))
+                    nvalid_y=int(r.nvalid_y), n_textured=int(r.n_textured), mean_dx=np.float32(r.mean_dx), mean_dy=np.float32(r.mean_dy))
 
     # -- misc
     def sync(self):

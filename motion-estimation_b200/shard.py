@@ -2,7 +2,7 @@
 
 The search has no inter-GPU data dependency: rank r takes a contiguous slice of the pair list,
 uploads only the frames that slice touches (its frame range plus the one-frame halo a pair needs),
-and searches it.  The only exchange is one ``all_gather`` of the per-pair records (24 bytes per
+and searches it.  The only exchange is one ``all_gather`` of the per-pair records (32 bytes per
 pair) so that every rank -- in particular rank 0, which runs the velocity arithmetic of
 estimate_vel_vid.py:540-573 -- sees the whole series.  NCCL over NVLink on GPUs, gloo in CPU tests.
 
@@ -16,7 +16,7 @@ from typing import Callable, List, Sequence, Tuple
 
 import numpy as np
 
-PAIR_FIELDS = 6   # pdx, pdy as float32 bit patterns; flag, nvalid_x, nvalid_y, reserved as int32
+PAIR_FIELDS = 8   # 32-byte records as int32 words (floats by bit pattern): pdx, pdy, flag, nvalid_x, nvalid_y, n_textured, mean_dx, mean_dy
 
 
 def shard_range(n_items: int, rank: int, world: int) -> Tuple[int, int]:
@@ -85,3 +85,123 @@ def search_pairs_sharded(frames: np.ndarray, pairs, search_local: Callable[[np.n
         rlo, rhi = shard_range(len(pairs), r, world)
         parts.append(out[r][: rhi - rlo].cpu().numpy())
     return int32_to_records(np.concatenate(parts, axis=0), record_dtype)
+
+
+# ------------------------------------------------------------------------------------------- GPU ranks
+def is_distributed() -> bool:
+    try:
+        import torch.distributed as dist
+    except ImportError:
+        return False
+    return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+
+
+class RecordGather:
+    """all_gather of pair records straight from device memory, off the search's critical path.
+
+    The records of a finished search are copied device-to-device into the send buffer on a side stream
+    (``me_copy_pair_records_device``, ordered after the search by an event), gathered with NCCL on that stream and
+    copied to pinned host memory there; ``wait()`` returns them.  Nothing blocks the stream the next search runs on,
+    so step k's records are gathered and consumed while step k+1 searches.  Two buffers alternate."""
+
+    def __init__(self, per_rank_pairs, record_dtype, group=None):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist, self.group, self.dtype = torch, dist, group, record_dtype
+        self.world = dist.get_world_size(group)
+        self.per = int(per_rank_pairs)
+        self.side = torch.cuda.Stream()
+        self.send = [torch.zeros((self.per, PAIR_FIELDS), dtype=torch.int32, device="cuda") for _ in range(2)]
+        self.recv = [torch.zeros((self.world, self.per, PAIR_FIELDS), dtype=torch.int32, device="cuda") for _ in range(2)]
+        self.host = [torch.zeros((self.world, self.per, PAIR_FIELDS), dtype=torch.int32).pin_memory() for _ in range(2)]
+        self.done = [torch.cuda.Event() for _ in range(2)]
+        self.k = 0
+
+    def start(self, est, n_pairs):
+        """Queue the gather of the records of est's last search; returns a ticket for wait()."""
+        b = self.k & 1
+        self.k += 1
+        if n_pairs:
+            est.copy_pair_records_device(self.send[b].data_ptr(), n_pairs, stream=self.side.cuda_stream)
+        with self.torch.cuda.stream(self.side):
+            self.dist.all_gather_into_tensor(self.recv[b], self.send[b], group=self.group)
+            self.host[b].copy_(self.recv[b], non_blocking=True)
+            self.done[b].record(self.side)
+        return b
+
+    def wait(self, ticket, counts=None):
+        """(world * per) records (or the first counts[r] of every rank, concatenated) as a structured array."""
+        self.done[ticket].synchronize()
+        a = self.host[ticket].numpy()
+        if counts is not None:
+            a = np.concatenate([a[r, :c] for r, c in enumerate(counts)], axis=0)
+        return int32_to_records(a.reshape(-1, PAIR_FIELDS).copy(), self.dtype)
+
+
+def search_consecutive_sharded(frames: np.ndarray, est_factory, record_dtype, chunk: int = 256, group=None) -> np.ndarray:
+    """Records of the consecutive pairs (k, k+1) of a host frame stack, searched on all ranks: rank r takes the
+    contiguous pair range shard_range(n - 1, r, world) and uploads only its frames plus the one-frame halo
+    (estimate_vel.py:377 -- strictly consecutive pairs are independent).  Every rank returns the whole series.
+
+    ``est_factory(max_frames, max_pairs)`` -> MotionEstimator on this rank's GPU."""
+    import torch.distributed as dist
+    n_pairs = len(frames) - 1
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    lo, hi = shard_range(n_pairs, rank, world)
+    per = -(-n_pairs // world)
+    chunk = max(1, min(chunk, per))
+    est = est_factory(chunk + 1, chunk)
+    gather = RecordGather(chunk, record_dtype, group)
+    rounds = -(-per // chunk)                       # every rank takes part in every collective, also with nothing left to search
+    tickets, parts = [], [[] for _ in range(world)]
+    for i in range(rounds):
+        k0 = lo + i * chunk
+        k1 = min(k0 + chunk, hi)
+        m = max(k1 - k0, 0)
+        if m:
+            est.upload(frames[k0:k1 + 1], first_slot=0)
+            est.launch([(j, j + 1) for j in range(m)])
+        tickets.append((gather.start(est, m), i))
+        if len(tickets) == 2:                       # consume round i-1 while round i searches
+            t, j = tickets.pop(0)
+            _collect(gather, t, j, chunk, n_pairs, world, parts)
+    for t, j in tickets:
+        _collect(gather, t, j, chunk, n_pairs, world, parts)
+    return np.concatenate([np.concatenate(p) if p else np.zeros(0, record_dtype) for p in parts])
+
+
+def _collect(gather, ticket, round_index, chunk, n_pairs, world, parts):
+    counts = []
+    for r in range(world):
+        rlo, rhi = shard_range(n_pairs, r, world)
+        k0 = rlo + round_index * chunk
+        counts.append(max(min(k0 + chunk, rhi) - k0, 0))
+    rec = gather.wait(ticket, counts)
+    o = 0
+    for r, c in enumerate(counts):
+        if c:
+            parts[r].append(rec[o:o + c])
+        o += c
+
+
+def gather_frames_sharded(local: "np.ndarray | None", est, first_slot, n_local, n_total, shape, group=None) -> np.ndarray:
+    """Reassemble a recording whose contiguous frame ranges were processed on different ranks: rank r holds n_local
+    frames in ring slots first_slot.. of `est`; returns the (n_total, H, W) host array on every rank.  The frames go
+    ring -> send buffer (device to device) -> NCCL all_gather -> one copy to the host."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    H, W = shape
+    per = -(-n_total // world)
+    send = torch.zeros((per, H, W), dtype=torch.uint8, device="cuda")
+    if n_local:
+        st = torch.cuda.current_stream().cuda_stream
+        est.copy_frames_device(send.data_ptr(), W, first_slot, n_local, stream=st)
+    recv = torch.empty((world, per, H, W), dtype=torch.uint8, device="cuda")
+    dist.all_gather_into_tensor(recv, send, group=group)
+    host = recv.cpu().numpy()
+    out = np.empty((n_total, H, W), np.uint8)
+    for r in range(world):
+        lo, hi = shard_range(n_total, r, world)
+        out[lo:hi] = host[r, :hi - lo]
+    return out

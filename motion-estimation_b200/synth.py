@@ -49,3 +49,27 @@ def translating_frames(n_frames, height, width, max_shift, seed_texture=0, seed_
         frames[k] = canvas[oy:oy + height, ox:ox + width]
     shifts = (e[:-1] - e[1:]).astype(np.int32)
     return frames, shifts
+
+
+def subpixel_sequence(n_frames, height, width, seed=5, step_lo=0.6, step_hi=2.4, y_amplitude=0.3):
+    """(frames (N,H,W) uint8, x (N,) float64, y (N,) float64): a clean texture translating with SUB-PIXEL motion.
+
+    Frame k shows one canvas displaced by (x[k], y[k]) full-resolution pixels (+x = content moves right), every frame
+    resampled from the canvas itself with a Lanczos kernel (no accumulated blur).  x advances by uniform random steps
+    in [step_lo, step_hi] px per frame, so the sub-pixel phases of the measured displacements are spread evenly; y is a
+    slow sinusoid of +-y_amplitude px.  Used by the velocity-accuracy tests: the true displacement between any two frames
+    is x[b] - x[a] exactly.
+    """
+    import cv2
+    rng = np.random.default_rng(seed)
+    x = np.concatenate([[0.0], np.cumsum(rng.uniform(step_lo, step_hi, n_frames - 1))])
+    y = y_amplitude * np.sin(np.arange(n_frames) * 0.21)
+    margin = int(x[-1]) + 16
+    canvas = texture(height + 16, width + margin + 16, seed).astype(np.float32)
+    frames = np.empty((n_frames, height, width), np.uint8)
+    for k in range(n_frames):
+        m = np.float32([[1, 0, margin + 8 - x[k]], [0, 1, 8 - y[k]]])          # dst(u, v) = canvas(u + m02, v + m12)
+        f = cv2.warpAffine(canvas, m, (width, height), flags=cv2.INTER_LANCZOS4 | cv2.WARP_INVERSE_MAP,
+                           borderMode=cv2.BORDER_REFLECT101)
+        frames[k] = np.clip(np.rint(f), 0, 255).astype(np.uint8)
+    return frames, x, y

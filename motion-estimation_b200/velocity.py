@@ -37,6 +37,11 @@ class PairLoopResult:
     pair_displacements: List[Tuple[float, float, int]] = field(default_factory=list)
     searches: int = 0                         # pair searches actually run (speculation included)
     launches: int = 0
+    # the reference's second opinion (:524-526): the frame mean of the dense field of EVERY compared pair
+    # (anchor, k), accepted or not, summed in full-resolution pixels; :582 prints it divided by pixels_per_mm
+    total_motion_optical_flow: float = 0.0
+    opt_flow_list: List[float] = field(default_factory=list)
+    final_position_dense: float = 0.0
 
     def as_tuple(self):
         return (self.out_information, self.velocity_list_x, self.velocity_list_y, self.tsList, self.motion_list_opt)
@@ -82,7 +87,8 @@ def anchored_pair_loop(n_frames: int, pair: Callable[[int, int], Tuple[float, fl
                        pixels_per_mm: float = PIXELS_PER_MM, gate_px: float = 2.0) -> PairLoopResult:
     """The video script's loop (estimate_vel_vid.py:493-583) over frames 0..n_frames-1.
 
-    ``pair(a, k)`` -> (pdx, pdy, measurement_flag); ``timestamp_ms(line_no)`` returns the value on
+    ``pair(a, k)`` -> (pdx, pdy, measurement_flag) or (pdx, pdy, measurement_flag, dense_mean_x) -- the fourth
+    value is what ``calculate_dense_flow`` returns first at :524; ``timestamp_ms(line_no)`` returns the value on
     1-based line ``line_no`` of the timestamp file, as ``linecache.getline`` does at :540-541.
     """
     out = PairLoopResult()
@@ -92,7 +98,11 @@ def anchored_pair_loop(n_frames: int, pair: Callable[[int, int], Tuple[float, fl
     anchor = 0
     timestamp_k += 1                         # :511, first frame only becomes the anchor
     for k in range(1, n_frames):
-        pdx, pdy, flag = pair(anchor, k)                                  # :522
+        r = pair(anchor, k)                                               # :522
+        pdx, pdy, flag = r[0], r[1], r[2]
+        if len(r) > 3:                                                     # :524-526, before the gate
+            out.total_motion_optical_flow += float(r[3])
+            out.opt_flow_list.append(out.total_motion_optical_flow)
         if pdx < gate_px and flag == 1:                                    # :531-534 anchor kept
             timestamp_k += 1
             continue
@@ -114,6 +124,7 @@ def anchored_pair_loop(n_frames: int, pair: Callable[[int, int], Tuple[float, fl
         out.pair_displacements.append((float(pdx), float(pdy), int(flag)))
         anchor = k                                                         # :575
         timestamp_k += 1                                                   # :577
+    out.final_position_dense = out.total_motion_optical_flow / pixels_per_mm   # :582
     return out
 
 

@@ -78,7 +78,7 @@ def search(prev, cur, block=16, rng=32, min_range=2, subpixel=True, min_valid=1,
     sad = np.zeros((nby, nbx), np.uint32)
     sub = np.zeros((nby, nbx, 2), np.float32)
     flags = np.zeros((nby, nbx), np.uint8)
-    pd = np.zeros(2, np.float32)
+    pd = np.zeros(4, np.float32)
     pi = np.zeros(4, np.int32)
     prm = Params(block, rng, min_range, int(bool(subpixel)), min_valid, min_curv)
     rc = lib().me_oracle_search(_p(prev, C.c_uint8), _p(cur, C.c_uint8), H, W, W, C.byref(prm),
@@ -88,16 +88,16 @@ def search(prev, cur, block=16, rng=32, min_range=2, subpixel=True, min_valid=1,
         raise ValueError(f"me_oracle_search rc={rc} (H={H} W={W} B={block} R={rng})")
     assert nb == mv.shape[0] * mv.shape[1]
     return dict(mv=mv, sad=sad, sub=sub, flags=flags, pdx=pd[0], pdy=pd[1], flag=int(pi[0]),
-                nvalid_x=int(pi[1]), nvalid_y=int(pi[2]))
+                nvalid_x=int(pi[1]), nvalid_y=int(pi[2]), n_textured=int(pi[3]), mean_dx=pd[2], mean_dy=pd[3])
 
 
 def search_pairs(frames, pairs, block=16, rng=32, min_range=2, subpixel=True, min_valid=1, min_curv=1, nthreads=0):
-    """(N,H,W) frames and a (P,2) list of (prev,cur) indices -> (P,2) float32 dxdy, (P,4) int32 (flag,nx,ny,0)."""
+    """(N,H,W) frames and a (P,2) list of (prev,cur) indices -> (P,4) float32 (pdx,pdy,mean_dx,mean_dy), (P,4) int32 (flag,nx,ny,n_textured)."""
     frames = np.ascontiguousarray(frames, dtype=np.uint8)
     pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
     N, H, W = frames.shape
     P = pairs.shape[0]
-    pd = np.zeros((P, 2), np.float32)
+    pd = np.zeros((P, 4), np.float32)
     pi = np.zeros((P, 4), np.int32)
     prm = Params(block, rng, min_range, int(bool(subpixel)), min_valid, min_curv)
     rc = lib().me_oracle_search_pairs(_p(frames, C.c_uint8), N, H, W, W, C.byref(prm), _p(pairs, C.c_int32), P,

@@ -96,5 +96,12 @@ def search(prev, cur, block=16, rng=32, min_range=2, subpixel=True, min_valid=1,
     pdx = _median_spec(sub[..., 0][valid[0]]) if nx else np.float32(0)
     pdy = _median_spec(sub[..., 1][valid[1]]) if ny else np.float32(0)
     flag = int(nx >= max(min_valid, 1))
+
+    def mean_spec(v):                       # exact fixed-point sum, one double division (spec: mean)
+        if v.size == 0:
+            return np.float32(0)
+        fixed = np.rint(v.astype(np.float32) * np.float32(1048576.0)).astype(np.int64)
+        return np.float32(np.float64(int(fixed.sum())) / (np.float64(v.size) * np.float64(1048576.0)))
     return dict(mv=mv, sad=best.astype(np.uint32), sub=sub, flags=flags, pdx=pdx, pdy=pdy, flag=flag,
-                nvalid_x=nx, nvalid_y=ny)
+                nvalid_x=nx, nvalid_y=ny, n_textured=int(textured.sum()),
+                mean_dx=mean_spec(sub[..., 0][valid[0]]), mean_dy=mean_spec(sub[..., 1][valid[1]]))

@@ -50,9 +50,19 @@
  *             flag = nvalid_x >= max(min_valid,1)  (x is the feed axis of the
  *             recordings; the reference gates on pdx, estimate_vel_vid.py:531).
  *             pdx = 0 when nvalid_x == 0, pdy = 0 when nvalid_y == 0.
+ *   mean      per axis, over the same valid blocks: S = sum of llrintf(sub * 2^20)
+ *             (exact 64-bit integer, order independent), mean = (float)((double)S /
+ *             ((double)n * 1048576.0)); 0 when n == 0.  This is the frame mean of the
+ *             dense per-block field, the role the reference gives its Farneback flow
+ *             (estimate_vel_vid.py:385-391).
+ *             n_textured = number of blocks with the textured bit: nvalid_x /
+ *             n_textured is the share of usable blocks whose minimum is a strict
+ *             interior peak, a confidence figure for the pair (it drops when the
+ *             motion leaves the search range).
  *
  * Build: see oracle/Makefile (gcc -O3 -fopenmp -shared -fPIC).
  */
+#include <math.h>
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
@@ -95,6 +105,10 @@ static int cmp_float(const void *a, const void *b)
 }
 
 /* median as the spec defines it; v is clobbered (sorted). n >= 1. */
+/* spec: mean -- a refined displacement as a 2^-20 fixed-point integer (the product is exact in binary32, the
+ * rounding is to nearest even), so that the sum over blocks is exact and independent of the order of addition */
+static int64_t spec_fixed(float v) { return (int64_t)llrintf(v * 1048576.0f); }
+
 static float spec_median(float *v, int n)
 {
     qsort(v, (size_t)n, sizeof(float), cmp_float);
@@ -134,8 +148,8 @@ int me_oracle_cost_surface(const uint8_t *prev, const uint8_t *cur, int H, int W
  *   blk_sad   uint32 [nb]     minimum SAD
  *   blk_sub   float  [nb][2]  refined (dx,dy)
  *   blk_flags uint8  [nb]
- * Per-pair outputs: pair_d[2] = (pdx,pdy) in full-resolution pixels,
- *                   pair_i[4] = (flag, nvalid_x, nvalid_y, 0).
+ * Per-pair outputs: pair_d[4] = (pdx, pdy, mean_dx, mean_dy) in full-resolution pixels,
+ *                   pair_i[4] = (flag, nvalid_x, nvalid_y, n_textured).
  * Any per-block pointer may be NULL.  Returns 0, or <0 on bad arguments.
  */
 int me_oracle_search(const uint8_t *prev, const uint8_t *cur, int H, int W, size_t pitch,
@@ -204,26 +218,30 @@ int me_oracle_search(const uint8_t *prev, const uint8_t *cur, int H, int W, size
         sx[b] = fx; sy[b] = fy;
         fl[b] = (uint8_t)flags;
     }
-    int nx = 0, ny = 0;
+    int nx = 0, ny = 0, ntex = 0;
+    int64_t fsx = 0, fsy = 0;        /* fixed-point sums of the valid refined displacements (spec: mean) */
     for (int b = 0; b < nb; ++b) {   /* in-place compaction: write index never passes read index */
         float vx = sx[b], vy = sy[b];
-        if ((fl[b] & (ME_FLAG_TEXTURED | ME_FLAG_X_PEAKED)) == (ME_FLAG_TEXTURED | ME_FLAG_X_PEAKED)) sx[nx++] = vx;
-        if ((fl[b] & (ME_FLAG_TEXTURED | ME_FLAG_Y_PEAKED)) == (ME_FLAG_TEXTURED | ME_FLAG_Y_PEAKED)) sy[ny++] = vy;
+        if (fl[b] & ME_FLAG_TEXTURED) ++ntex;
+        if ((fl[b] & (ME_FLAG_TEXTURED | ME_FLAG_X_PEAKED)) == (ME_FLAG_TEXTURED | ME_FLAG_X_PEAKED)) { sx[nx++] = vx; fsx += spec_fixed(vx); }
+        if ((fl[b] & (ME_FLAG_TEXTURED | ME_FLAG_Y_PEAKED)) == (ME_FLAG_TEXTURED | ME_FLAG_Y_PEAKED)) { sy[ny++] = vy; fsy += spec_fixed(vy); }
     }
     int need = p->min_valid > 1 ? p->min_valid : 1;
     pair_d[0] = nx > 0 ? spec_median(sx, nx) : 0.0f;
     pair_d[1] = ny > 0 ? spec_median(sy, ny) : 0.0f;
+    pair_d[2] = nx > 0 ? (float)((double)fsx / ((double)nx * 1048576.0)) : 0.0f;
+    pair_d[3] = ny > 0 ? (float)((double)fsy / ((double)ny * 1048576.0)) : 0.0f;
     pair_i[0] = nx >= need;
     pair_i[1] = nx;
     pair_i[2] = ny;
-    pair_i[3] = 0;
+    pair_i[3] = ntex;
     free(sx); free(fl);
     return 0;
 }
 
 /*
  * Batch form used for timing and for the anchored pair loop: frames is (N,H,pitch),
- * pairs is P x (prev_index, cur_index).  Per-pair outputs only: pair_d (P,2), pair_i (P,4).
+ * pairs is P x (prev_index, cur_index).  Per-pair outputs only: pair_d (P,4), pair_i (P,4).
  */
 int me_oracle_search_pairs(const uint8_t *frames, int N, int H, int W, size_t pitch,
                            const me_oracle_params *p, const int32_t *pairs, int P,
@@ -233,7 +251,7 @@ int me_oracle_search_pairs(const uint8_t *frames, int N, int H, int W, size_t pi
         int a = pairs[2 * k], c = pairs[2 * k + 1];
         if (a < 0 || a >= N || c < 0 || c >= N) return -3;
         int rc = me_oracle_search(frames + (size_t)a * H * pitch, frames + (size_t)c * H * pitch, H, W,
-                                  pitch, p, NULL, NULL, NULL, NULL, pair_d + 2 * k, pair_i + 4 * k, nthreads);
+                                  pitch, p, NULL, NULL, NULL, NULL, pair_d + 4 * k, pair_i + 4 * k, nthreads);
         if (rc) return rc;
     }
     return 0;

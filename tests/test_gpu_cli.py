@@ -40,25 +40,27 @@ def recording(tmp_path):
 def test_estimate_vel_vid_cli(recording, tmp_path):
     d, frames = recording
     out = tmp_path / "out"
-    res = _load("estimate_vel_vid").main(["0", "20", "-p", d, "--out", str(out), "--units", "fullres", "--range", "16"])
+    res = _load("estimate_vel_vid").main(["0", "20", "-p", d, "--out", str(out), "--units", "fullres", "--range", "16", "--no-preprocess"])
     rows = list(csv.reader(open(out / "velocity_estimates.csv")))
     assert rows[0] == ["Timestamp [s]", "mm/min X-axis optical", "mm/min Y-axis optical"]
     assert len(rows) - 1 == len(res.out_information) == 19                 # every pair moves 7 px >= the gate of 2
     vx = np.array([float(r[0]) for r in rows[1:]])
     want = (7.0 / 611) / (5.531e-3 / 60)                                    # 7 px per 5.531 ms
     np.testing.assert_allclose(vx[1:], want, rtol=0.01)                     # row 0 is measured from t = 0 like the reference
-    ref_units = _load("estimate_vel_vid").main(["0", "20", "-p", d, "--out", str(out), "--range", "16"])
+    ref_units = _load("estimate_vel_vid").main(["0", "20", "-p", d, "--out", str(out), "--range", "16", "--no-preprocess"])
     np.testing.assert_allclose([r[0] for r in ref_units.out_information][1:], want / 2, rtol=0.01)   # half-resolution unit
 
 
-def test_estimate_vel_vid_cli_preprocess(recording, tmp_path):
-    """--preprocess = the reference's default pipeline: CLAHE, non-local means, then the pair loop; the cache it
-    leaves (images.npy, the role of images.h5) holds what cv2 produces from the same frames, and -c reuses it."""
+def test_estimate_vel_vid_cli_default_is_the_reference_pipeline(recording, tmp_path):
+    """The plain command line does what the reference's main() does (its lines 697-709): CLAHE, non-local means, then the
+    pair loop.  The cache it leaves (images.h5 ['clean_images'] with h5py, else images.npy) holds what cv2 produces from
+    the same frames, -c reuses it, and the explicit --preprocess of earlier versions gives the same CSV."""
     import cv2
     d, frames = recording
     out = tmp_path / "out3"
-    res = _load("estimate_vel_vid").main(["0", "14", "-p", d, "--out", str(out), "--units", "fullres", "--range", "16", "--preprocess"])
-    clean = np.load(os.path.join(d, "images.npy"))
+    mod = _load("estimate_vel_vid")
+    res = mod.main(["0", "14", "-p", d, "--out", str(out), "--units", "fullres", "--range", "16"])
+    clean = mod.load_cache(os.path.join(d, "images.h5"), os.path.join(d, "images.npy"))
     assert clean.shape == (14, 64, 320)
     clahe = cv2.createCLAHE(clipLimit=2.0, tileGridSize=(8, 8))
     eq = np.stack([clahe.apply(z) for z in frames[:14]])
@@ -68,8 +70,13 @@ def test_estimate_vel_vid_cli_preprocess(recording, tmp_path):
         np.testing.assert_array_equal(clean[k], want, err_msg=f"frame {k}")
     want_v = (7.0 / 611) / (5.531e-3 / 60)
     np.testing.assert_allclose([r[0] for r in res.out_information][1:], want_v, rtol=0.02)
-    again = _load("estimate_vel_vid").main(["0", "14", "-p", d, "--out", str(out), "--units", "fullres", "--range", "16", "-c"])
+    csv_default = open(out / "velocity_estimates.csv").read()
+    again = mod.main(["0", "14", "-p", d, "--out", str(out), "--units", "fullres", "--range", "16", "-c"])
     assert [tuple(r) for r in again.out_information] == [tuple(r) for r in res.out_information]
+    mod.main(["0", "14", "-p", d, "--out", str(tmp_path / "out4"), "--units", "fullres", "--range", "16", "--preprocess"])
+    assert open(tmp_path / "out4" / "velocity_estimates.csv").read() == csv_default
+    fast = mod.main(["0", "14", "-p", d, "--out", str(tmp_path / "out5"), "--units", "fullres", "--range", "16", "--no-preprocess"])
+    assert len(fast.out_information) == len(res.out_information)
 
 
 def test_estimate_vel_cli(recording, tmp_path):

@@ -24,8 +24,8 @@ def check_pair(est, idx, prev, cur, cfg, rec):
     g = est.fetch_blocks(idx)
     for k in KEYS:
         np.testing.assert_array_equal(g[k], o[k], err_msg=f"{k} (pair {idx})")
-    assert (rec["pdx"], rec["pdy"], rec["flag"], rec["nvalid_x"], rec["nvalid_y"]) == \
-           (o["pdx"], o["pdy"], o["flag"], o["nvalid_x"], o["nvalid_y"])
+    assert (rec["pdx"], rec["pdy"], rec["flag"], rec["nvalid_x"], rec["nvalid_y"], rec["n_textured"], rec["mean_dx"], rec["mean_dy"]) == \
+           (o["pdx"], o["pdy"], o["flag"], o["nvalid_x"], o["nvalid_y"], o["n_textured"], o["mean_dx"], o["mean_dy"])
 
 
 CASES = [
@@ -289,6 +289,41 @@ def test_4k_properties(me):
         for i, (dx, dy) in enumerate(shifts):
             assert res[i]["flag"] == 1 and res[i]["pdx"] == dx and res[i]["pdy"] == dy
         _sample_blocks_equal_oracle(est, 1, frames[1], frames[2], 8, 64, [(0, 0), (479, 269), (240, 135), (7, 262)])
+
+
+def _noisy_translating_frames(n, H, W, max_shift, seed):
+    """Translating texture plus independent per-frame noise: the SAD minima are not exact zeros, so the sub-pixel fit,
+    the peak gates and the median all have real work to do."""
+    from motion_estimation_b200 import synth
+    frames, shifts = synth.translating_frames(n, H, W, max_shift, seed_texture=seed, seed_motion=seed + 1)
+    noise = np.random.default_rng(seed + 2).integers(-6, 7, size=frames.shape)
+    return np.clip(frames.astype(np.int16) + noise, 0, 255).astype(np.uint8), shifts
+
+
+def test_full_hd_every_block_and_the_fused_median_with_subpixel(me):
+    """configs[2] at full size with the sub-pixel path on: ALL 8040 blocks of two 1920x1080 pairs (vectors, SADs, refined
+    vectors, flags) and the pair records (3-level radix-select median, mean, counts) equal the oracle, through the resident
+    kernel (1005 units per pair) and, for the second pair alone, through one CTA per tile."""
+    frames, shifts = _noisy_translating_frames(3, 1080, 1920, 32, seed=21)
+    cfg = me.SearchConfig(block=16, range=32)
+    with me.MotionEstimator(1080, 1920, cfg, max_frames=3, max_pairs=2) as est:
+        est.upload(frames)
+        res = est.search([(0, 1), (1, 2)])
+        for i in range(2):
+            check_pair(est, i, frames[i], frames[i + 1], cfg, res[i])
+            assert res[i]["nvalid_x"] > 7000 and abs(res[i]["pdx"] - shifts[i][0]) < 0.2 and abs(res[i]["pdy"] - shifts[i][1]) < 0.2
+
+
+def test_4k_every_block_with_subpixel(me):
+    """configs[3] at full size: all 129 600 blocks of a 3840x2160 pair, 8x8 blocks, +-64 px (slabbed candidate square,
+    resident kernel), sub-pixel path on, against the oracle (about a second of host time on the box's cores)."""
+    frames, shifts = _noisy_translating_frames(2, 2160, 3840, 64, seed=22)
+    cfg = me.SearchConfig(block=8, range=64)
+    with me.MotionEstimator(2160, 3840, cfg, max_frames=2, max_pairs=1) as est:
+        est.upload(frames)
+        res = est.search([(0, 1)])
+        check_pair(est, 0, frames[0], frames[1], cfg, res[0])
+        assert res[0]["nvalid_x"] > 100000 and abs(res[0]["pdx"] - shifts[0][0]) < 0.2
 
 
 def _fuzz_case(seed):

@@ -14,7 +14,7 @@ KEYS = ("mv", "sad", "sub", "flags")
 def assert_same(a, b):
     for k in KEYS:
         np.testing.assert_array_equal(a[k], b[k], err_msg=k)
-    for k in ("pdx", "pdy", "flag", "nvalid_x", "nvalid_y"):
+    for k in ("pdx", "pdy", "flag", "nvalid_x", "nvalid_y", "n_textured", "mean_dx", "mean_dy"):
         assert a[k] == b[k], k
 
 

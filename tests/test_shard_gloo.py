@@ -17,7 +17,8 @@ def _local_search(frames_slice, local_pairs):
     pd, pi = sad.search_pairs(frames_slice, local_pairs, 16, 8)
     rec = np.zeros(len(local_pairs), PAIR_DTYPE)
     rec["pdx"], rec["pdy"] = pd[:, 0], pd[:, 1]
-    rec["flag"], rec["nvalid_x"], rec["nvalid_y"] = pi[:, 0], pi[:, 1], pi[:, 2]
+    rec["flag"], rec["nvalid_x"], rec["nvalid_y"], rec["n_textured"] = pi[:, 0], pi[:, 1], pi[:, 2], pi[:, 3]
+    rec["mean_dx"], rec["mean_dy"] = pd[:, 2], pd[:, 3]
     return rec
 
 

@@ -42,7 +42,7 @@ def test_static_scratch_entry_point_equals_context_entry_point(me):
         for call, (seed, pairs) in enumerate([(0, [(0, 1), (1, 2), (2, 3)]), (7, [(3, 0), (2, 1), (0, 2), (1, 1)])]):
             frames, _ = synth.translating_frames(4, H, W, 14, seed_texture=seed, seed_motion=seed + 1)
             t = torch.from_numpy(frames).cuda().contiguous()
-            out = torch.zeros(len(pairs) * 6, dtype=torch.int32, device="cuda")     # 24-byte records
+            out = torch.zeros(len(pairs) * 8, dtype=torch.int32, device="cuda")     # 32-byte records
             assert _static_search(me, t, pairs, cfg, out, stream) == 0, me._lib.lib().me_last_error()
             torch.cuda.synchronize()
             got = out.cpu().numpy().view(me.PAIR_DTYPE)
@@ -65,7 +65,7 @@ def test_static_scratch_with_candidate_slabs(me):
     with me.MotionEstimator(H, W, cfg, max_frames=2, max_pairs=2) as est:
         assert est.geometry["slabs_x"] * est.geometry["slabs_y"] > 1
         for _ in range(2):
-            out = torch.zeros(len(pairs) * 6, dtype=torch.int32, device="cuda")
+            out = torch.zeros(len(pairs) * 8, dtype=torch.int32, device="cuda")
             assert _static_search(me, t, pairs, cfg, out, stream) == 0, me._lib.lib().me_last_error()
             torch.cuda.synchronize()
             est.search_device(t.data_ptr(), t.stride(1), t.shape[0], pairs, stream=stream)
@@ -85,7 +85,7 @@ def test_static_scratch_with_multi_row_tiles(me):
     with me.MotionEstimator(H, W, cfg, max_frames=3, max_pairs=4) as est:
         assert est.geometry["tile_blocks_y"] > 1
         for _ in range(2):
-            out = torch.zeros(len(pairs) * 6, dtype=torch.int32, device="cuda")
+            out = torch.zeros(len(pairs) * 8, dtype=torch.int32, device="cuda")
             assert _static_search(me, t, pairs, cfg, out, stream) == 0, me._lib.lib().me_last_error()
             torch.cuda.synchronize()
             est.search_device(t.data_ptr(), t.stride(1), t.shape[0], pairs, stream=stream)
@@ -98,7 +98,7 @@ def test_static_scratch_rejects_oversized_requests(me):
     cfg = me.SearchConfig(block=8, range=8)
     H, W = 1080, 1920                                     # 32 400 blocks x 17 B per pair: 8 pairs do not fit 4 MiB
     t = torch.zeros((2, H, W), dtype=torch.uint8, device="cuda")
-    out = torch.zeros(8 * 6, dtype=torch.int32, device="cuda")
+    out = torch.zeros(8 * 8, dtype=torch.int32, device="cuda")
     rc = _static_search(me, t, [(0, 1)] * 8, cfg, out, torch.cuda.current_stream().cuda_stream)
     assert rc == -1
     msg = L.me_last_error().decode()
