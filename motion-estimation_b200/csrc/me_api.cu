@@ -153,6 +153,10 @@ struct me_ctx {
     size_t d_luts_bytes = 0;
     uint8_t *d_nlm = nullptr;           // denoised frames + accumulators + tables of me_denoise, allocated on first use
     size_t d_nlm_bytes = 0;
+    int *d_nlm_meta = nullptr;          // weight tables + per-frame table index of me_denoise
+    size_t d_nlm_meta_bytes = 0;
+    std::vector<int> nlm_meta;          // what they were built for: (n_frames, windows, h, temporal windows); same again = reuse
+    int nlm_meta_shift = 0;
     // streams / events
     cudaStream_t s_copy = nullptr, s_compute = nullptr;
     cudaEvent_t ev_upload = nullptr, ev_search = nullptr, ev_k0 = nullptr, ev_k1 = nullptr;
@@ -709,7 +713,7 @@ int me_destroy(me_ctx *c)
     cudaSetDevice(c->device);
     if (c->s_copy) cudaStreamSynchronize(c->s_copy);
     if (c->s_compute) cudaStreamSynchronize(c->s_compute);
-    cudaFree(c->d_frames); cudaFree(c->d_bgr); cudaFree(c->d_luts); cudaFree(c->d_nlm); cudaFree(c->d_pairs);
+    cudaFree(c->d_frames); cudaFree(c->d_bgr); cudaFree(c->d_luts); cudaFree(c->d_nlm); cudaFree(c->d_nlm_meta); cudaFree(c->d_pairs);
     cudaFree(c->args.blk_mv); cudaFree(c->args.blk_sad); cudaFree(c->args.blk_sub); cudaFree(c->args.blk_flags);
     cudaFree(c->args.pair_out); cudaFree(c->args.pair_ticket); cudaFree(c->args.blk_key); cudaFree(c->args.tile_ticket);
     cudaFree(c->d_ready); cudaFree(c->d_error);
@@ -823,21 +827,45 @@ int me_denoise(me_ctx *c, int first_slot, int n_frames, const int32_t *temporal_
     }
     CU_TRY(cudaSetDevice(c->device));
 
-    // weight tables, one per distinct temporal window
-    std::vector<int> luts, off(n_frames), len(n_frames);
-    std::vector<std::pair<int, std::pair<int, int>>> seen;
-    int shift = 0;
-    for (int k = 0; k < n_frames; ++k) {
-        const int t = temporal_window[k];
-        if (t == 0) { off[k] = len[k] = 0; continue; }
-        bool found = false;
-        for (auto &e : seen) if (e.first == t) { off[k] = e.second.first; len[k] = e.second.second; found = true; }
-        if (found) continue;
-        std::vector<int> tab;
-        nlm_weight_table(h, tws, sws, t, tab, shift);
-        off[k] = (int)luts.size(); len[k] = (int)tab.size();
-        seen.push_back({t, {off[k], len[k]}});
-        luts.insert(luts.end(), tab.begin(), tab.end());
+    // Weight tables, one per distinct temporal window, + the per-frame table index: [twin | lut_off | lut_len | luts] in a
+    // device buffer of their own.  The same call as last time (a recording is denoised chunk after chunk with the same
+    // windows) finds them there: no rebuild (46k exp() per table), no upload, no stream synchronisation.
+    std::vector<int> key;
+    key.push_back(n_frames); key.push_back(tws); key.push_back(sws);
+    { int hb; memcpy(&hb, &h, sizeof hb); key.push_back(hb); }
+    key.insert(key.end(), temporal_window, temporal_window + n_frames);
+    int shift = c->nlm_meta_shift;
+    if (key != c->nlm_meta) {
+        std::vector<int> luts, off(n_frames), len(n_frames);
+        std::vector<std::pair<int, std::pair<int, int>>> seen;
+        for (int k = 0; k < n_frames; ++k) {
+            const int t = temporal_window[k];
+            if (t == 0) { off[k] = len[k] = 0; continue; }
+            bool found = false;
+            for (auto &e : seen) if (e.first == t) { off[k] = e.second.first; len[k] = e.second.second; found = true; }
+            if (found) continue;
+            std::vector<int> tab;
+            nlm_weight_table(h, tws, sws, t, tab, shift);
+            off[k] = (int)luts.size(); len[k] = (int)tab.size();
+            seen.push_back({t, {off[k], len[k]}});
+            luts.insert(luts.end(), tab.begin(), tab.end());
+        }
+        std::vector<int> meta;
+        meta.insert(meta.end(), temporal_window, temporal_window + n_frames);
+        meta.insert(meta.end(), off.begin(), off.end());
+        meta.insert(meta.end(), len.begin(), len.end());
+        meta.insert(meta.end(), luts.begin(), luts.end());
+        const size_t meta_bytes = meta.size() * sizeof(int);
+        CU_TRY(cudaStreamSynchronize(c->s_copy));    // an earlier call may still read the old tables; meta is pageable host memory
+        if (c->d_nlm_meta_bytes < meta_bytes) {
+            if (c->d_nlm_meta) CU_TRY(cudaFree(c->d_nlm_meta));
+            c->d_nlm_meta = nullptr; c->d_nlm_meta_bytes = 0;
+            CU_TRY(cudaMalloc(&c->d_nlm_meta, meta_bytes));
+            c->d_nlm_meta_bytes = meta_bytes;
+        }
+        CU_TRY(cudaMemcpy(c->d_nlm_meta, meta.data(), meta_bytes, cudaMemcpyHostToDevice));
+        c->nlm_meta = key;
+        c->nlm_meta_shift = shift;
     }
 
     me::NlmArgs a{};
@@ -855,11 +883,10 @@ int me_denoise(me_ctx *c, int first_slot, int n_frames, const int32_t *temporal_
     a.nsplit = env_int("ME_NLM_SPLIT", a.nsplit);
     if (a.nsplit < 1) a.nsplit = 1;
 
-    // device scratch: [dst frames | acc | twin | lut_off | lut_len | luts]
+    // device scratch: [dst frames | acc]
     const size_t dst_bytes = (size_t)n_frames * c->H * c->pitch;
     const size_t acc_bytes = a.nsplit > 1 ? (size_t)n_frames * c->H * c->W * 8 : 0;
-    const size_t meta_bytes = (3 * (size_t)n_frames + luts.size()) * 4;
-    const size_t need = align_up(dst_bytes, 256) + align_up(acc_bytes, 256) + meta_bytes;
+    const size_t need = align_up(dst_bytes, 256) + align_up(acc_bytes, 256);
     if (c->d_nlm_bytes < need) {
         CU_TRY(cudaStreamSynchronize(c->s_copy));
         if (c->d_nlm) CU_TRY(cudaFree(c->d_nlm));
@@ -869,19 +896,11 @@ int me_denoise(me_ctx *c, int first_slot, int n_frames, const int32_t *temporal_
     }
     a.dst = c->d_nlm;
     a.acc = reinterpret_cast<int *>(c->d_nlm + align_up(dst_bytes, 256));
-    int *d_meta = reinterpret_cast<int *>(c->d_nlm + align_up(dst_bytes, 256) + align_up(acc_bytes, 256));
-    std::vector<int> meta;
-    meta.insert(meta.end(), temporal_window, temporal_window + n_frames);
-    meta.insert(meta.end(), off.begin(), off.end());
-    meta.insert(meta.end(), len.begin(), len.end());
-    meta.insert(meta.end(), luts.begin(), luts.end());
+    const int *d_meta = c->d_nlm_meta;
     a.twin = d_meta; a.lut_off = d_meta + n_frames; a.lut_len = d_meta + 2 * n_frames; a.luts = d_meta + 3 * n_frames;
 
     for (auto &r : c->recent)                        // the frames are rewritten in place: wait for searches that read them
         if (r.used && r.lo < first_slot + n_frames && r.hi >= first_slot) CU_TRY(cudaStreamWaitEvent(c->s_copy, r.done, 0));
-    CU_TRY(cudaStreamSynchronize(c->s_copy));        // meta is pageable host memory: keep the copy below synchronous with it
-    CU_TRY(cudaMemcpyAsync(d_meta, meta.data(), meta_bytes, cudaMemcpyHostToDevice, c->s_copy));
-    CU_TRY(cudaStreamSynchronize(c->s_copy));
     if (a.nsplit > 1) CU_TRY(cudaMemsetAsync(a.acc, 0, acc_bytes, c->s_copy));
     const dim3 grid((unsigned)ceil_div(c->W, me::kNlmTW), (unsigned)ceil_div(c->H, me::kNlmTR), (unsigned)(n_frames * a.nsplit));
     int rc = tws == 19 ? nlm_launch<19>(a, grid, smem, c->s_copy) : nlm_launch<7>(a, grid, smem, c->s_copy);

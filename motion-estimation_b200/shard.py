@@ -114,7 +114,7 @@ class RecordGather:
         self.send = [torch.zeros((self.per, PAIR_FIELDS), dtype=torch.int32, device="cuda") for _ in range(2)]
         self.recv = [torch.zeros((self.world, self.per, PAIR_FIELDS), dtype=torch.int32, device="cuda") for _ in range(2)]
         self.host = [torch.zeros((self.world, self.per, PAIR_FIELDS), dtype=torch.int32).pin_memory() for _ in range(2)]
-        self.done = [torch.cuda.Event() for _ in range(2)]
+        self.done = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
         self.k = 0
 
     def start(self, est, n_pairs):
