@@ -457,9 +457,11 @@ def run_clip(args, rk):
     frames, x = clip_recording(N, seed=11 + rk.rank)                    # one recording per GPU (recordings are what shards)
     stamps = [FRAME_DT_MS * k for k in range(N + 3)]
     cfg = api.default_config
+    if os.environ.get("ME_BENCH_RANGE_Y"):              # experiments: a rectangular search window (the recordings move along x)
+        cfg = me.SearchConfig(cfg.block, cfg.range, range_y=int(os.environ["ME_BENCH_RANGE_Y"]))
     peaks, peak_src = read_measured_peaks()
     peak_alu, sms, ipc, f_max = alu_peak(me, rk.local, peaks, None)
-    api.set_defaults(device=rk.local)
+    api.set_defaults(config=cfg, device=rk.local)
 
     # ---- value: frames resident in the ring, the anchor walk inside the library (me_anchored_scan), device-timed
     est = me.MotionEstimator(64, 640, cfg, max_frames=N + 1, max_pairs=256, device=rk.local)

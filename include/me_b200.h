@@ -59,6 +59,8 @@ typedef struct me_params {
     int32_t subpixel;   /* 0 = integer displacements only                                     */
     int32_t min_valid;  /* pair flag = nvalid_x >= max(min_valid, 1)                          */
     int32_t min_curv;   /* peak gate on cm - 2 c0 + cp; values < 1 mean 1                     */
+    int32_t range_y;    /* Ry: vertical range, 1 .. range; 0 = the same as range (square search).  The
+                           example recordings move along x only: a small Ry cuts the work accordingly */
 } me_params;
 
 /* One record per frame pair: replaces the (pdx, pdy, measurement_flag) tuple returned at

@@ -29,7 +29,7 @@ class MEError(RuntimeError):
 
 class Params(C.Structure):
     _fields_ = [("block", C.c_int32), ("range", C.c_int32), ("min_range", C.c_int32),
-                ("subpixel", C.c_int32), ("min_valid", C.c_int32), ("min_curv", C.c_int32)]
+                ("subpixel", C.c_int32), ("min_valid", C.c_int32), ("min_curv", C.c_int32), ("range_y", C.c_int32)]
 
 
 class PairResult(C.Structure):

@@ -196,7 +196,9 @@ int configure(me_ctx *c)
     const int B = c->p.block, R = c->p.range, U = 2 * R + 1, W = c->W, H = c->H;
     const int MB = B < 16 ? 16 : B, NSUB = MB / B, NDY = kNDY, NQ = kNQ;
     me::SearchArgs &a = c->args;
+    const int Ry = (c->p.range_y > 0 && c->p.range_y < R) ? c->p.range_y : R, Uy = 2 * Ry + 1;
     a.W = W; a.H = H; a.R = R; a.U = U;
+    a.Ry = Ry; a.Uy = Uy; a.dy0 = R - Ry;
     a.nbx = W / B; a.nby = H / B; a.nb = a.nbx * a.nby;
     a.nmbx = ceil_div(a.nbx, NSUB);
     a.frame_pitch = (int)c->pitch;
@@ -233,12 +235,12 @@ int configure(me_ctx *c)
         if (forced_nsx && nsx != forced_nsx) continue;
         const int wmax = U - (nsx - 1) * su;                        // the last slab is the widest
         for (int tsy = 1; tsy <= 16; ++tsy) {
-            int sd = tsy == 1 ? U : (U / tsy) / NDY * NDY;
+            int sd = tsy == 1 ? Uy : (Uy / tsy) / NDY * NDY;
             if (sd < NDY && tsy > 1) break;
-            const int nsy = tsy == 1 ? 1 : U / sd;
+            const int nsy = tsy == 1 ? 1 : Uy / sd;
             if (tsy > 1 && nsy != tsy) continue;
             if (forced_nsy && nsy != forced_nsy) continue;
-            const int hmax = U - (nsy - 1) * sd;
+            const int hmax = Uy - (nsy - 1) * sd;
             // Block rows per tile: more than one only without slabs (a small range leaves little work per row,
             // and the window's 2R halo rows are then shared by the rows of the tile).
             for (int tmr = 1; tmr <= (nsx * nsy == 1 ? 8 : 1); ++tmr) {
@@ -363,7 +365,7 @@ int configure(me_ctx *c)
         // tools/cmp_persist.sh, one-row tiles): wins from a ratio of about 1.7 -- 16x16 +-32 +2.5 %, +-48 +4.6 %,
         // +-64 (2x3 slabs) +2.3 %, 4K +-64 +4.5 %; 8x8 +-32 +2.5 %, +-48 +8 %, 4K +-64 (1x2 slabs) +9 %; 32x32 +-32
         // +2 %, +-40 +12 % -- and loses below it (8x8 +-24: -13 %, 16x16 +-20: -2 %).
-        const double cand = (double)U * U / (a.nsx * a.nsy);                                             // candidates of an average slab
+        const double cand = (double)U * Uy / (a.nsx * a.nsy);                                             // candidates of an average slab
         const double t_cons = (double)a.tmb * NSUB * cand * B * B / 256.0;                               // cycles at 64 lanes x 4 px
         const double build = (double)a.n_row_boxes * a.box_rows * (c->win_pitch / 16) / 32.0 * 120.0 / me::kProducerWarps;
         const double t_prod = 6000.0 + build * (a.x_off == 0 ? 1.0 : (a.x_off & 3) ? 3.0 : 1.5);   // whole-word offsets skip the selects
@@ -374,7 +376,7 @@ int configure(me_ctx *c)
     {   // fastdiv magics of full slabs (see sad_search.cuh)
         auto magic = [](int d) { return d <= 1 ? 0u : (unsigned)(0x100000000ull / (unsigned)d + 1ull); };
         for (int ly = 0; ly < 2; ++ly) {
-            const int h = ly == 0 ? (a.nsy > 1 ? a.sd : U) : U - (a.nsy - 1) * a.sd;
+            const int h = ly == 0 ? (a.nsy > 1 ? a.sd : Uy) : Uy - (a.nsy - 1) * a.sd;
             a.full_nd[ly] = ceil_div(h, NDY);
             a.magic_nd[ly] = magic(a.full_nd[ly]);
             for (int lx = 0; lx < 2; ++lx) {
@@ -387,7 +389,7 @@ int configure(me_ctx *c)
 
     // Threads: whole multiples of 4 warps so that every scheduler of the SM gets the same number of warps
     // (r01 sweep: 224 threads = 7 warps ran 13 % slower than 128 or 256).
-    const int total = a.tmb * a.tmr * ceil_div(U - (a.nsy - 1) * a.sd, NDY) * a.n_wide[1];
+    const int total = a.tmb * a.tmr * ceil_div(Uy - (a.nsy - 1) * a.sd, NDY) * a.n_wide[1];
     c->threads = env_int("ME_THREADS", total >= 384 ? 256 : 128);
     if (c->threads % 32 || c->threads < 32 || c->threads > c->kc.maxt)
         return fail(ME_EINVAL, "ME_THREADS=%d is not a multiple of 32 in [32,%d]", c->threads, c->kc.maxt);
@@ -395,11 +397,11 @@ int configure(me_ctx *c)
     a.repeat = env_int("ME_REPEAT", 1) > 0 ? env_int("ME_REPEAT", 1) : 1;
 
     // Work accounting: nominal = what the ALU executes, valid = in-frame candidates.
-    c->cand_px = (long long)a.nb * B * B * U * U;
+    c->cand_px = (long long)a.nb * B * B * U * Uy;
     long long valid = 0;
     for (int by = 0; by < a.nby; ++by) {
         const int y0 = by * B;
-        const int ny = (R < H - B - y0 ? R : H - B - y0) - (-R > -y0 ? -R : -y0) + 1;
+        const int ny = (Ry < H - B - y0 ? Ry : H - B - y0) - (-Ry > -y0 ? -Ry : -y0) + 1;
         long long sx = 0;
         for (int bx = 0; bx < a.nbx; ++bx) {
             const int x0 = bx * B;
@@ -592,6 +594,7 @@ int me_create(int device, int height, int width, const me_params *params, int ma
     const int B = params->block, R = params->range;
     if (B != 8 && B != 16 && B != 32) return fail(ME_EUNSUPPORTED, "block size %d: built sizes are 8, 16, 32", B);
     if (R < 1) return fail(ME_EINVAL, "range %d < 1", R);
+    if (params->range_y < 0 || params->range_y > R) return fail(ME_EINVAL, "range_y %d outside 0..range (%d); 0 means the same as range", params->range_y, R);
     if (height < B || width < B) return fail(ME_EINVAL, "frame %dx%d smaller than one %d-pixel block", width, height, B);
     if (max_frames < 2 || max_pairs < 1) return fail(ME_EINVAL, "max_frames >= 2 and max_pairs >= 1 required");
     int ndev = 0;
@@ -609,10 +612,13 @@ int me_create(int device, int height, int width, const me_params *params, int ma
     c->sm_count = prop.multiProcessorCount;
     c->pitch = (size_t)round_up(width, 16);
     c->frame_stride = c->pitch * (size_t)height;
-    c->plan_pairs = max_pairs > 4 ? 4 : max_pairs;      // small frames: tiles small enough that a few pairs fill the GPU
+    {   // small frames: tiles small enough that a batch of a few pairs (the anchored scan's usual two or three) fills the GPU
+        const int few = env_int("ME_PLAN_PAIRS", 2);
+        c->plan_pairs = max_pairs > few ? few : max_pairs;
+    }
     int rc = configure(c);
     if (rc) { delete c; return rc; }
-    if (max_pairs > 4) {
+    if (max_pairs > c->plan_pairs) {
         // ... and a second plan for launches of many pairs, where bigger tiles fill it as well (the 640x64 recordings: 2-block
         // tiles for 4 pairs, 8-block tiles for 64).  Kept only when it differs.
         me_ctx *b = new me_ctx();
@@ -1293,6 +1299,7 @@ extern "C" int me_search_static_scratch(const uint8_t *d_frames, size_t pitch, i
     const int B = params->block, R = params->range;
     if (B != 8 && B != 16 && B != 32) return fail(ME_EUNSUPPORTED, "block size %d: built sizes are 8, 16, 32", B);
     if (R < 1) return fail(ME_EINVAL, "range %d < 1", R);
+    if (params->range_y < 0 || params->range_y > R) return fail(ME_EINVAL, "range_y %d outside 0..range (%d); 0 means the same as range", params->range_y, R);
     if (height < B || width < B) return fail(ME_EINVAL, "frame %dx%d smaller than one %d-pixel block", width, height, B);
     if ((reinterpret_cast<uintptr_t>(d_frames) & 15) || pitch % 16 || pitch < (size_t)width)
         return fail(ME_EINVAL, "device frames need a 16-byte aligned base and a pitch >= width that is a multiple of 16");

@@ -96,11 +96,11 @@ __device__ __forceinline__ UnitInfo decode_unit(const SearchArgs &a, int u)
     ui.nj = min(a.tmb, a.nmbx - ui.tx * a.tmb);
     ui.nblk = min(ui.nj * G::NSUB, a.nbx - ui.tx * a.tmb * G::NSUB);
     ui.ubase = sx * a.su;
-    ui.dbase = sy * a.sd;
+    ui.dbase = a.dy0 + sy * a.sd;
     ui.lastx = sx == a.nsx - 1;
     const int lasty = sy == a.nsy - 1;
     ui.slab_w = ui.lastx ? a.U - ui.ubase : a.su;
-    const int slab_h = lasty ? a.U - ui.dbase : a.sd;
+    const int slab_h = lasty ? a.dy0 + a.Uy - ui.dbase : a.sd;
     const int twoR = 2 * a.R;
     ui.dyi_lo = max(0, a.R - ui.Y0 - ui.dbase);
     ui.dyi_hi = min(slab_h - 1, min(twoR, a.R + a.H - B - ui.Y0) - ui.dbase);

@@ -59,6 +59,7 @@ struct SearchArgs {
     // block grid
     int nbx, nby, nb;
     int R, U;                   // U = 2R + 1
+    int Ry, Uy, dy0;            // vertical range Ry <= R: Uy = 2Ry + 1 rows of the candidate square are searched, from dy index dy0 = R - Ry
     int tmb, tiles_x, tiles_per_pair;   // macro-blocks per tile row
     int tmr;                    // block rows per tile (> 1 only for single-slab plans with little work per row: small ranges)
     unsigned magic_nj[2];       // fastdiv by the macro-blocks of a tile row, [last tile in x]
@@ -374,7 +375,7 @@ __device__ __forceinline__ void finalize_block(const SearchArgs &a, int pair, co
     const int dyi = (int)(rank / (uint32_t)U), ui = (int)rank - dyi * U;
     const int dx = ui - R, dy = dyi - R;
     const int dxlo = max(-R, -x0), dxhi = min(R, a.W - B - x0);
-    const int dylo = max(-R, -y0), dyhi = min(R, a.H - B - y0);
+    const int dylo = max(-a.Ry, -y0), dyhi = min(a.Ry, a.H - B - y0);
     const bool xin = dx - 1 >= dxlo && dx + 1 <= dxhi;
     const bool yin = dy - 1 >= dylo && dy + 1 <= dyhi;
     const size_t pitch = (size_t)a.frame_pitch;
@@ -411,13 +412,13 @@ __device__ __forceinline__ void finalize_block_smem(const SearchArgs &a, int pai
     const int dyi = (int)(rank / (uint32_t)U), ui = (int)rank - dyi * U;
     const int dx = ui - R, dy = dyi - R;
     const int dxlo = max(-R, -x0), dxhi = min(R, a.W - B - x0);
-    const int dylo = max(-R, -y0), dyhi = min(R, a.H - B - y0);
+    const int dylo = max(-a.Ry, -y0), dyhi = min(a.Ry, a.H - B - y0);
     const bool xin = dx - 1 >= dxlo && dx + 1 <= dxhi;
     const bool yin = dy - 1 >= dylo && dy + 1 <= dyhi;
     const size_t cstride = (size_t)a.copy_bytes + kCopySkew;
-    // word pointers of the candidate (u, dyi) = copy u & 3, row dyi + jr*B, word jb*SW + (u >> 2)
+    // word pointers of the candidate (u, dyi) = copy u & 3, row dyi - dy0 + jr*B (the window starts at dy index dy0), word jb*SW + (u >> 2)
     auto cand = [&](int u, int d) {
-        return reinterpret_cast<const uint32_t *>(s_win + (size_t)(u & 3) * cstride) + (d + jr * B) * PW + jb * SW + (u >> 2);
+        return reinterpret_cast<const uint32_t *>(s_win + (size_t)(u & 3) * cstride) + (d - a.dy0 + jr * B) * PW + jb * SW + (u >> 2);
     };
     const uint32_t *ref = reinterpret_cast<const uint32_t *>(s_ref) + jr * B * RPW + jb * SW;
     const uint32_t *cxm = cand(xin ? ui - 1 : ui, dyi), *cxp = cand(xin ? ui + 1 : ui, dyi);
@@ -460,9 +461,78 @@ __device__ __forceinline__ void pair_keys(const uint8_t *fl, const float2 *sub, 
     ky = (f & (ME_FLAG_TEXTURED | ME_FLAG_Y_PEAKED)) == (ME_FLAG_TEXTURED | ME_FLAG_Y_PEAKED) ? fkey(v.y) : kNoKey;
 }
 
+// Few blocks per pair (the 640x64 recordings have 160): the three radix passes, each clearing and scanning 2 x 2048 bins,
+// are a fixed ~10 us at the tail of every launch of the anchored scan, which waits for exactly that.  Here every thread
+// ranks its own keys by counting the smaller ones (ties by block index) in shared memory: one pass, two barriers.
+constexpr int kSmallNb = 512;
+static __device__ void reduce_pair_small(const SearchArgs &a, int pair, unsigned *scratch)
+{
+    uint32_t *kx = scratch, *ky = scratch + kSmallNb;
+    unsigned *bc = scratch + 2 * kSmallNb;       // [0],[1] lower / upper middle key x; [2],[3] y; [4] textured; [5],[6] counts; [8..11] field sums
+    const uint8_t *fl = a.blk_flags + (size_t)pair * a.nb;
+    const float2 *sub = reinterpret_cast<const float2 *>(a.blk_sub) + (size_t)pair * a.nb;
+    const int T = blockDim.x, tid = threadIdx.x, nb = a.nb;
+    if (tid < 12) bc[tid] = 0;
+    __syncthreads();
+    unsigned ntex = 0, nx = 0, ny = 0;
+    long long fsx = 0, fsy = 0;
+    for (int b = tid; b < nb; b += T) {
+        uint32_t x, y;
+        unsigned tex;
+        float2 v;
+        pair_keys(fl, sub, b, x, y, tex, v);
+        kx[b] = x; ky[b] = y;
+        ntex += tex;
+        if (x != kNoKey) { ++nx; fsx += (long long)__float2ll_rn(__fmul_rn(v.x, 1048576.0f)); }
+        if (y != kNoKey) { ++ny; fsy += (long long)__float2ll_rn(__fmul_rn(v.y, 1048576.0f)); }
+    }
+    ntex = __reduce_add_sync(kFull, ntex); nx = __reduce_add_sync(kFull, nx); ny = __reduce_add_sync(kFull, ny);
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        fsx += __shfl_xor_sync(kFull, fsx, o);
+        fsy += __shfl_xor_sync(kFull, fsy, o);
+    }
+    if ((tid & 31) == 0) {
+        if (ntex) atomicAdd(&bc[4], ntex);
+        if (nx) atomicAdd(&bc[5], nx);
+        if (ny) atomicAdd(&bc[6], ny);
+        if (fsx) atomicAdd(reinterpret_cast<unsigned long long *>(bc + 8), (unsigned long long)fsx);
+        if (fsy) atomicAdd(reinterpret_cast<unsigned long long *>(bc + 10), (unsigned long long)fsy);
+    }
+    __syncthreads();
+    const unsigned cx = bc[5], cy = bc[6];
+    for (int b = tid; b < nb; b += T) {
+        const uint32_t x = kx[b], y = ky[b];
+        unsigned rx = 0, ry = 0;
+        for (int j = 0; j < nb; ++j) {           // broadcast reads: every thread looks at the same j
+            const uint32_t xj = kx[j], yj = ky[j];
+            rx += (xj != kNoKey) & ((xj < x) | ((xj == x) & (j < b)));
+            ry += (yj != kNoKey) & ((yj < y) | ((yj == y) & (j < b)));
+        }
+        if (x != kNoKey) { if (rx == (cx - 1) / 2) bc[0] = x; if (rx == cx / 2) bc[1] = x; }
+        if (y != kNoKey) { if (ry == (cy - 1) / 2) bc[2] = y; if (ry == cy / 2) bc[3] = y; }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        me_pair_result r;
+        r.pdx = cx ? __fmul_rn(0.5f, __fadd_rn(funkey(bc[0]), funkey(bc[1]))) : 0.0f;
+        r.pdy = cy ? __fmul_rn(0.5f, __fadd_rn(funkey(bc[2]), funkey(bc[3]))) : 0.0f;
+        r.flag = (int)cx >= (a.min_valid > 1 ? a.min_valid : 1);
+        r.nvalid_x = (int)cx;
+        r.nvalid_y = (int)cy;
+        r.n_textured = (int)bc[4];
+        const long long sx = *reinterpret_cast<const long long *>(bc + 8), sy = *reinterpret_cast<const long long *>(bc + 10);
+        r.mean_dx = cx ? (float)__ddiv_rn((double)sx, __dmul_rn((double)cx, 1048576.0)) : 0.0f;
+        r.mean_dy = cy ? (float)__ddiv_rn((double)sy, __dmul_rn((double)cy, 1048576.0)) : 0.0f;
+        a.pair_out[pair] = r;
+        a.pair_ticket[pair] = 0;                    // leave the scratch clean for the next launch
+    }
+}
+
 // scratch: the CTA's shared memory from offset 0 (at least 2*kSelBins*4 + 128 bytes)
 static __device__ void reduce_pair(const SearchArgs &a, int pair, unsigned *scratch)
 {
+    if (a.nb <= kSmallNb) { reduce_pair_small(a, pair, scratch); return; }     // uniform across the CTA
     unsigned *hist = scratch;                    // [2][kSelBins]
     unsigned *bc = scratch + 2 * kSelBins;       // per axis: [0] chosen bin, [1] rank inside it, [2] its count, [3] total; [8],[9] next keys; [10] textured; [12..15] field sums
     const uint8_t *fl = a.blk_flags + (size_t)pair * a.nb;
@@ -718,9 +788,9 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     const int tr = tile_id - pair * a.tiles_per_pair;
     const int ty = tr / a.tiles_x, tx = tr - ty * a.tiles_x;
     const int sy = slab / a.nsx, sx = slab - sy * a.nsx;
-    const int ubase = sx * a.su, dbase = sy * a.sd;
+    const int ubase = sx * a.su, dbase = a.dy0 + sy * a.sd;
     const int lastx = sx == a.nsx - 1;
-    const int slab_w = lastx ? a.U - ubase : a.su, slab_h = (sy == a.nsy - 1) ? a.U - dbase : a.sd;
+    const int slab_w = lastx ? a.U - ubase : a.su, slab_h = (sy == a.nsy - 1) ? a.dy0 + a.Uy - dbase : a.sd;
     const int prev_slot = __ldg(a.pairs + 2 * pair), cur_slot = __ldg(a.pairs + 2 * pair + 1);
     const int tmr = MR ? a.tmr : 1;
     const int X0 = tx * a.tmb * G::MB, Y0 = ty * tmr * B;

@@ -31,9 +31,10 @@ class SearchConfig:
     subpixel: bool = True
     min_valid: int = 1
     min_curv: int = 1
+    range_y: int = 0          # vertical range, 0 = the same as range; the recordings move along x only
 
     def as_struct(self) -> Params:
-        return Params(self.block, self.range, self.min_range, int(self.subpixel), self.min_valid, self.min_curv)
+        return Params(self.block, self.range, self.min_range, int(self.subpixel), self.min_valid, self.min_curv, self.range_y)
 
 
 class MotionEstimator:

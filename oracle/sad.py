@@ -19,7 +19,7 @@ FLAG_Y_PEAKED = 16
 
 class Params(C.Structure):
     _fields_ = [("block", C.c_int32), ("range", C.c_int32), ("min_range", C.c_int32),
-                ("subpixel", C.c_int32), ("min_valid", C.c_int32), ("min_curv", C.c_int32)]
+                ("subpixel", C.c_int32), ("min_valid", C.c_int32), ("min_curv", C.c_int32), ("range_y", C.c_int32)]
 
 
 def build(force: bool = False) -> str:
@@ -66,7 +66,7 @@ def _frame(a):
     return a
 
 
-def search(prev, cur, block=16, rng=32, min_range=2, subpixel=True, min_valid=1, min_curv=1, nthreads=0):
+def search(prev, cur, block=16, rng=32, min_range=2, subpixel=True, min_valid=1, min_curv=1, nthreads=0, range_y=0):
     """One frame pair through the C oracle.  Returns a dict of per-block and per-pair results."""
     prev, cur = _frame(prev), _frame(cur)
     if prev.shape != cur.shape:
@@ -80,7 +80,7 @@ def search(prev, cur, block=16, rng=32, min_range=2, subpixel=True, min_valid=1,
     flags = np.zeros((nby, nbx), np.uint8)
     pd = np.zeros(4, np.float32)
     pi = np.zeros(4, np.int32)
-    prm = Params(block, rng, min_range, int(bool(subpixel)), min_valid, min_curv)
+    prm = Params(block, rng, min_range, int(bool(subpixel)), min_valid, min_curv, range_y)
     rc = lib().me_oracle_search(_p(prev, C.c_uint8), _p(cur, C.c_uint8), H, W, W, C.byref(prm),
                                 _p(mv, C.c_int16), _p(sad, C.c_uint32), _p(sub, C.c_float),
                                 _p(flags, C.c_uint8), _p(pd, C.c_float), _p(pi, C.c_int32), nthreads)
@@ -91,7 +91,7 @@ def search(prev, cur, block=16, rng=32, min_range=2, subpixel=True, min_valid=1,
                 nvalid_x=int(pi[1]), nvalid_y=int(pi[2]), n_textured=int(pi[3]), mean_dx=pd[2], mean_dy=pd[3])
 
 
-def search_pairs(frames, pairs, block=16, rng=32, min_range=2, subpixel=True, min_valid=1, min_curv=1, nthreads=0):
+def search_pairs(frames, pairs, block=16, rng=32, min_range=2, subpixel=True, min_valid=1, min_curv=1, nthreads=0, range_y=0):
     """(N,H,W) frames and a (P,2) list of (prev,cur) indices -> (P,4) float32 (pdx,pdy,mean_dx,mean_dy), (P,4) int32 (flag,nx,ny,n_textured)."""
     frames = np.ascontiguousarray(frames, dtype=np.uint8)
     pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
@@ -99,7 +99,7 @@ def search_pairs(frames, pairs, block=16, rng=32, min_range=2, subpixel=True, mi
     P = pairs.shape[0]
     pd = np.zeros((P, 4), np.float32)
     pi = np.zeros((P, 4), np.int32)
-    prm = Params(block, rng, min_range, int(bool(subpixel)), min_valid, min_curv)
+    prm = Params(block, rng, min_range, int(bool(subpixel)), min_valid, min_curv, range_y)
     rc = lib().me_oracle_search_pairs(_p(frames, C.c_uint8), N, H, W, W, C.byref(prm), _p(pairs, C.c_int32), P,
                                       _p(pd, C.c_float), _p(pi, C.c_int32), nthreads)
     if rc:

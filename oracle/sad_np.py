@@ -16,7 +16,7 @@ FLAG_Y_PEAKED = 16
 _INF = np.iinfo(np.int64).max
 
 
-def cost_volume(prev, cur, block, rng):
+def cost_volume(prev, cur, block, rng, range_y=0):
     """(nby, nbx, 2R+1, 2R+1) int64 SAD volume indexed [by, bx, dy+R, dx+R]; out-of-domain = _INF."""
     prev = np.asarray(prev, np.uint8).astype(np.int64)
     cur = np.asarray(cur, np.uint8).astype(np.int64)
@@ -28,7 +28,8 @@ def cost_volume(prev, cur, block, rng):
     ys = np.arange(nby) * B
     xs = np.arange(nbx) * B
     ref = prev[: nby * B, : nbx * B].reshape(nby, B, nbx, B)
-    for dy in range(-R, R + 1):
+    Ry = range_y if range_y > 0 else R
+    for dy in range(-Ry, Ry + 1):
         oky = (ys + dy >= 0) & (ys + dy + B <= H)
         if not oky.any():
             continue
@@ -53,9 +54,9 @@ def _median_spec(v):
     return np.float32(0.5) * np.float32(s[(n - 1) // 2] + s[n // 2])
 
 
-def search(prev, cur, block=16, rng=32, min_range=2, subpixel=True, min_valid=1, min_curv=1):
+def search(prev, cur, block=16, rng=32, min_range=2, subpixel=True, min_valid=1, min_curv=1, range_y=0):
     prev = np.asarray(prev, np.uint8)
-    vol = cost_volume(prev, cur, block, rng)
+    vol = cost_volume(prev, cur, block, rng, range_y)
     nby, nbx, U, _ = vol.shape
     B, R = block, rng
     min_curv = max(int(min_curv), 1)

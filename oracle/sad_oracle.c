@@ -21,7 +21,8 @@
  *             ragged right/bottom strip is not searched).  Block (bx,by) has its
  *             top-left pixel at (x0,y0) = (bx*B, by*B) in the PREVIOUS frame.
  *   cost      SAD(dx,dy) = sum_{i,j<B} | cur[y0+dy+i][x0+dx+j] - prev[y0+i][x0+j] |
- *   domain    dx,dy in [-R,R] and the displaced block must lie wholly inside the
+ *   domain    dx in [-R,R], dy in [-Ry,Ry] (Ry = R unless range_y names a smaller vertical
+ *             range: the recordings move along x only) and the displaced block must lie wholly inside the
  *             frame: 0 <= x0+dx, x0+dx+B <= W, 0 <= y0+dy, y0+dy+B <= H.
  *             (0,0) is always in the domain.  No padding pixels are invented.
  *   argmin    first minimum in raster order, dy outer ascending, dx inner
@@ -84,6 +85,7 @@ typedef struct {
     int32_t subpixel;   /* 0 = integer only */
     int32_t min_valid;  /* pair accepted when nvalid_x >= max(min_valid,1) */
     int32_t min_curv;   /* peak gate on den = cm - 2 c0 + cp; values < 1 are treated as 1 */
+    int32_t range_y;    /* Ry: vertical range, 1..R; 0 = R (square search) */
 } me_oracle_params;
 
 static inline uint32_t block_sad(const uint8_t *a, size_t pa, const uint8_t *b, size_t pb, int B)
@@ -156,8 +158,8 @@ int me_oracle_search(const uint8_t *prev, const uint8_t *cur, int H, int W, size
                      const me_oracle_params *p, int16_t *blk_mv, uint32_t *blk_sad, float *blk_sub,
                      uint8_t *blk_flags, float *pair_d, int32_t *pair_i, int nthreads)
 {
-    const int B = p->block, R = p->range;
-    if (B < 4 || B > 64 || (B & 3) || R < 1 || R > 128 || H < B || W < B || pitch < (size_t)W) return -1;
+    const int B = p->block, R = p->range, Ry = p->range_y > 0 ? p->range_y : p->range;
+    if (B < 4 || B > 64 || (B & 3) || R < 1 || R > 128 || Ry > R || H < B || W < B || pitch < (size_t)W) return -1;
     const int nbx = W / B, nby = H / B, nb = nbx * nby;
     const int32_t min_curv = p->min_curv < 1 ? 1 : p->min_curv;
     float *sx = (float *)malloc(sizeof(float) * (size_t)nb * 2);
@@ -175,7 +177,7 @@ int me_oracle_search(const uint8_t *prev, const uint8_t *cur, int H, int W, size
         const uint8_t *ref = prev + (size_t)y0 * pitch + x0;
         /* domain (an axis-aligned box of displacements) */
         const int dxlo = (-R > -x0) ? -R : -x0, dxhi = (R < W - B - x0) ? R : W - B - x0;
-        const int dylo = (-R > -y0) ? -R : -y0, dyhi = (R < H - B - y0) ? R : H - B - y0;
+        const int dylo = (-Ry > -y0) ? -Ry : -y0, dyhi = (Ry < H - B - y0) ? Ry : H - B - y0;
         uint32_t best = UINT32_MAX;
         int bdx = 0, bdy = 0;
         for (int dy = dylo; dy <= dyhi; ++dy)

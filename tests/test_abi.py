@@ -26,7 +26,7 @@ def test_header_symbols_are_exported(me):
 
 def test_struct_layouts_match_the_header(me):
     assert C.sizeof(me._lib.PairResult) == 32 and me.PAIR_DTYPE.itemsize == 32
-    assert C.sizeof(me._lib.Params) == 24
+    assert C.sizeof(me._lib.Params) == 28
     assert me._lib.Geometry.cand_px_per_pair.offset % 8 == 0
 
 

@@ -20,7 +20,7 @@ KEYS = ("mv", "sad", "sub", "flags")
 
 def check_pair(est, idx, prev, cur, cfg, rec):
     o = osad.search(prev, cur, cfg.block, cfg.range, min_range=cfg.min_range, subpixel=cfg.subpixel,
-                    min_valid=cfg.min_valid, min_curv=cfg.min_curv)
+                    min_valid=cfg.min_valid, min_curv=cfg.min_curv, range_y=cfg.range_y)
     g = est.fetch_blocks(idx)
     for k in KEYS:
         np.testing.assert_array_equal(g[k], o[k], err_msg=f"{k} (pair {idx})")
@@ -291,6 +291,28 @@ def test_4k_properties(me):
         _sample_blocks_equal_oracle(est, 1, frames[1], frames[2], 8, 64, [(0, 0), (479, 269), (240, 135), (7, 262)])
 
 
+@pytest.mark.parametrize("H,W,B,R,Ry", [(64, 640, 16, 64, 8), (64, 640, 16, 32, 4), (270, 480, 16, 32, 3), (136, 256, 8, 64, 10),
+                                        (144, 320, 16, 128, 16), (96, 160, 32, 16, 15), (72, 200, 8, 12, 1), (720, 1280, 16, 8, 2),
+                                        (160, 192, 16, 100, 40)])
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_rectangular_range_equals_oracle(me, monkeypatch, H, W, B, R, Ry, mode):
+    """range_y < range: only |dy| <= Ry is searched (the recordings move along x).  Same spec otherwise; default plan,
+    resident kernel forced, one CTA per tile forced."""
+    from motion_estimation_b200 import synth
+    if mode:
+        monkeypatch.setenv("ME_PERSISTENT", "2" if mode == 1 else "0")
+    frames, _ = synth.translating_frames(4, H, W, min(2 * Ry, R, 20), seed_texture=H + Ry, seed_motion=W + R)
+    cfg = me.SearchConfig(block=B, range=R, range_y=Ry)
+    pairs = [(0, 1), (1, 2), (2, 3), (3, 0), (1, 1)]
+    with me.MotionEstimator(H, W, cfg, max_frames=4, max_pairs=len(pairs)) as est:
+        est.upload(frames)
+        res = est.search(pairs)
+        for i in (0, 3, 4) if H >= 700 else range(len(pairs)):
+            check_pair(est, i, frames[pairs[i][0]], frames[pairs[i][1]], cfg, res[i])
+        one = est.search([pairs[3]])                      # a one-pair launch takes the small-batch plan
+        assert one[0].tobytes() == res[3].tobytes()
+
+
 def _noisy_translating_frames(n, H, W, max_shift, seed):
     """Translating texture plus independent per-frame noise: the SAD minima are not exact zeros, so the sub-pixel fit,
     the peak gates and the median all have real work to do."""
@@ -337,6 +359,7 @@ def _fuzz_case(seed):
     n_pairs = int(rng.choice([1, 2, 5, 24]))
     mode = int(rng.integers(0, 3))          # 0 default plan, 1 resident kernel forced, 2 one CTA per tile forced
     kw = dict(subpixel=bool(rng.integers(0, 2)), min_range=int(rng.choice([0, 2, 30])), min_curv=int(rng.choice([1, 50])))
+    kw["range_y"] = int(rng.choice([0, 0, 1, max(1, R // 4), max(1, R - 1)]))       # rectangular search windows now and then
     return H, W, B, R, n_pairs, mode, kw
 
 

@@ -33,6 +33,19 @@ def test_c_oracle_equals_numpy_restatement(H, W, B, R, mc):
     assert_same(sad.search(prev, cur, B, R, min_range=4, min_curv=mc), sad_np.search(prev, cur, B, R, min_range=4, min_curv=mc))
 
 
+@pytest.mark.parametrize("H,W,B,R,Ry", [(64, 160, 16, 24, 3), (64, 640, 16, 64, 8), (40, 96, 8, 12, 1), (96, 96, 32, 20, 20)])
+def test_rectangular_range_c_oracle_equals_numpy_restatement(H, W, B, R, Ry):
+    """range_y: |dy| <= Ry < R (the recordings move along x); same spec otherwise, same raster-order tie-break."""
+    rng = np.random.default_rng(H + W + Ry)
+    a = textured(rng, H, W)
+    prev, cur = a[32:32 + H, 32:32 + W], a[31:31 + H, 27:27 + W]      # content moves (+5, +1)
+    c, n = sad.search(prev, cur, B, R, range_y=Ry), sad_np.search(prev, cur, B, R, range_y=Ry)
+    assert_same(c, n)
+    assert np.abs(c["mv"][..., 1]).max() <= Ry
+    if Ry == R:
+        assert_same(c, sad.search(prev, cur, B, R))
+
+
 def test_integer_only_mode():
     rng = np.random.default_rng(5)
     a = textured(rng, 48, 64)
