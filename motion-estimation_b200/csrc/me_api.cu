@@ -157,6 +157,7 @@ struct me_ctx {
     size_t d_nlm_meta_bytes = 0;
     std::vector<int> nlm_meta;          // what they were built for: (n_frames, windows, h, temporal windows); same again = reuse
     int nlm_meta_shift = 0;
+    bool nlm_lut_small = false;
     // streams / events
     cudaStream_t s_copy = nullptr, s_compute = nullptr;
     cudaEvent_t ev_upload = nullptr, ev_search = nullptr, ev_k0 = nullptr, ev_k1 = nullptr;
@@ -570,11 +571,11 @@ void nlm_weight_table(float h, int tws, int sws, int n_frames, std::vector<int> 
     table.resize((size_t)last + 1);
 }
 
-template <int TWS> int nlm_launch(const me::NlmArgs &a, dim3 grid, size_t smem, cudaStream_t s)
+template <int TWS, int SH, bool LS> int nlm_launch(const me::NlmArgs &a, dim3 grid, size_t smem, cudaStream_t s)
 {
-    int rc = raise_smem_limit((const void *)me::nlm_kernel<TWS>, false);
+    int rc = raise_smem_limit((const void *)me::nlm_kernel<TWS, SH, LS>, false);
     if (rc) return rc;
-    me::nlm_kernel<TWS><<<grid, me::kNlmThreads, smem, s>>>(a);
+    me::nlm_kernel<TWS, SH, LS><<<grid, me::kNlmThreads, smem, s>>>(a);
     CU_TRY(cudaGetLastError());
     return ME_OK;
 }
@@ -855,6 +856,7 @@ int me_denoise(me_ctx *c, int first_slot, int n_frames, const int32_t *temporal_
             off[k] = (int)luts.size(); len[k] = (int)tab.size();
             seen.push_back({t, {off[k], len[k]}});
             luts.insert(luts.end(), tab.begin(), tab.end());
+            luts.push_back(0);                       // entry [len]: the kernel clamps the table index instead of testing it
         }
         std::vector<int> meta;
         meta.insert(meta.end(), temporal_window, temporal_window + n_frames);
@@ -872,17 +874,19 @@ int me_denoise(me_ctx *c, int first_slot, int n_frames, const int32_t *temporal_
         CU_TRY(cudaMemcpy(c->d_nlm_meta, meta.data(), meta_bytes, cudaMemcpyHostToDevice));
         c->nlm_meta = key;
         c->nlm_meta_shift = shift;
+        c->nlm_lut_small = true;                     // every table short enough and every weight 16-bit: shared-memory form usable
+        for (int k = 0; k < n_frames; ++k) if (len[k] + 1 > me::kNlmLutSmem) c->nlm_lut_small = false;
+        for (int w : luts) if (w > 65535) c->nlm_lut_small = false;
     }
 
     me::NlmArgs a{};
     a.src = c->d_frames; a.frame_stride = (long long)c->frame_stride; a.pitch = (int)c->pitch; a.W = c->W; a.H = c->H;
     a.first_slot = first_slot; a.sh = sh; a.shift = shift;
     const int b = sh + th;
-    a.itp = (me::kNlmTW + 2 * b + 3) / 4 * 4;
-    if ((a.itp / 4) % 2 == 0) a.itp += 4;                       // odd word pitch: lanes on consecutive rows hit distinct banks
+    a.itp = me::nlm_region_pitch(sh, th);
     a.it_rows = me::kNlmTR + 2 * b;
     const int nr = me::kNlmTR + 2 * th;
-    const size_t smem = (size_t)nr * (me::kNlmTW + 4) * 4 + (size_t)a.it_rows * a.itp + 16;
+    const size_t smem = 2 * (size_t)nr * (me::kNlmTW + 4) * 4 + (size_t)a.it_rows * a.itp + 16;   // two buffers of horizontal sums + the region
     const int tiles = ceil_div(c->W, me::kNlmTW) * ceil_div(c->H, me::kNlmTR);
     a.nsplit = 1;
     if ((long long)tiles * n_frames < 2ll * c->sm_count) a.nsplit = std::min(sws, (int)ceil_div(2 * c->sm_count, tiles * n_frames));
@@ -909,7 +913,11 @@ int me_denoise(me_ctx *c, int first_slot, int n_frames, const int32_t *temporal_
         if (r.used && r.lo < first_slot + n_frames && r.hi >= first_slot) CU_TRY(cudaStreamWaitEvent(c->s_copy, r.done, 0));
     if (a.nsplit > 1) CU_TRY(cudaMemsetAsync(a.acc, 0, acc_bytes, c->s_copy));
     const dim3 grid((unsigned)ceil_div(c->W, me::kNlmTW), (unsigned)ceil_div(c->H, me::kNlmTR), (unsigned)(n_frames * a.nsplit));
-    int rc = tws == 19 ? nlm_launch<19>(a, grid, smem, c->s_copy) : nlm_launch<7>(a, grid, smem, c->s_copy);
+    // the reference's windows (19 / 41) with a table that fits 16-bit shared-memory entries take the specialised instantiation
+    const bool lut_smem = tws == 19 && sh == 20 && c->nlm_lut_small;
+    int rc = tws == 19 ? (lut_smem ? nlm_launch<19, 20, true>(a, grid, smem + 2 * me::kNlmLutSmem, c->s_copy)
+                                   : nlm_launch<19, 0, false>(a, grid, smem, c->s_copy))
+                       : nlm_launch<7, 0, false>(a, grid, smem, c->s_copy);
     if (rc) return rc;
     c->launches += 1;
     if (a.nsplit > 1) {

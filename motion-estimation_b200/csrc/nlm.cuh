@@ -49,25 +49,50 @@ __device__ __forceinline__ int reflect101_iter(int p, int n)
 
 constexpr int kNlmK = 32, kNlmRS = 2, kNlmTW = 128, kNlmTR = kNlmK * kNlmRS, kNlmS = 16, kNlmThreads = 256;
 
-template <int TWS>
+// Shared-region row pitch for a search half-size: whole words, an odd number of them (lanes on consecutive rows hit distinct banks).
+__host__ __device__ constexpr int nlm_region_pitch(int sh, int th)
+{
+    int p = (kNlmTW + 2 * (sh + th) + 3) / 4 * 4;
+    return (p / 4) % 2 == 0 ? p + 4 : p;
+}
+__host__ __device__ constexpr int nlm_shift(int tws)            // OpenCV: dist >> shift with 2^shift >= template area
+{
+    int s = 0;
+    while ((1 << s) < tws * tws) ++s;
+    return s;
+}
+
+// SH > 0: the search half-size is a compile-time constant (the reference's 41-pixel window: SH = 20), so the region pitch
+// and every row offset are immediates; SH = 0 reads them from the arguments (other window sizes).
+//
+// Schedule: the horizontal pass of offset k+1 and the vertical pass of offset k run between the same two barriers
+// (two buffers of horizontal sums), so an offset costs one __syncthreads instead of two and a thread's light and heavy
+// phases even out (r02 ncu of the two-barrier form: 0.51 barrier stalls per issued instruction, 59.7 % issue-active).
+// LS: the frame's weight table is staged in shared memory as 16-bit entries (the host checks that it fits: the
+// reference's parameters give weights <= 5009 and ~1100 entries): a table read is then SHF + VIMNMX + LDS instead of a
+// 64-bit address computation and a global load (r02b ncu: 4 of 25.5 thread-instructions per offset and pixel).
+constexpr int kNlmLutSmem = 1280;          // entries of the shared-memory table (2.5 KB)
+template <int TWS, int SH, bool LS>
 __global__ void __launch_bounds__(kNlmThreads, 2) nlm_kernel(const NlmArgs a)
 {
     constexpr int TH = TWS / 2, K = kNlmK, TW = kNlmTW, TR = kNlmTR, NR = TR + 2 * TH, S = kNlmS, NSEG = TW / S,
                   NTASK = NSEG * NR, ROUNDS = (NTASK + kNlmThreads - 1) / kNlmThreads, NPX = S + TWS - 1, NW = (NPX + 3) / 4,
                   HP = TW + 4;                                   // HP = 4 mod 32: conflict-free STS.128 from lanes on consecutive rows
+    constexpr int SHIFT = nlm_shift(TWS);
     extern __shared__ __align__(16) unsigned char nlm_smem[];
-    int *s_h = reinterpret_cast<int *>(nlm_smem);                // NR x HP horizontal sums
-    unsigned char *s_it = nlm_smem + NR * HP * 4;               // it_rows x itp displaced-frame region
+    int *s_h0 = reinterpret_cast<int *>(nlm_smem);              // 2 x (NR x HP) horizontal sums
+    unsigned char *s_it = nlm_smem + 2 * NR * HP * 4;           // it_rows x itp displaced-frame region
+    unsigned short *s_lut = reinterpret_cast<unsigned short *>(nlm_smem + 2 * NR * HP * 4 + a.it_rows * a.itp);   // LS only
 
     const int tid = threadIdx.x;
     const int n = blockIdx.z / a.nsplit, sp = blockIdx.z - n * a.nsplit;
     const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TR;
-    const int sh = a.sh, sws = 2 * sh + 1, b = sh + TH;
+    const int sh = SH > 0 ? SH : a.sh, sws = 2 * sh + 1, b = sh + TH;
+    const int itp = SH > 0 ? nlm_region_pitch(SH, TH) : a.itp, it_rows = TR + 2 * b, itw = itp >> 2;
     const int T = a.twin[n], half = T / 2;
     const int *lut = a.luts + a.lut_off[n];
-    const int lut_n = a.lut_len[n];
+    const int lut_n = a.lut_len[n];                              // lut[lut_n] == 0: indices are clamped, not tested
     const uint8_t *main_f = a.src + (long long)(a.first_slot + n) * a.frame_stride;
-    const int itw = a.itp >> 2;
 
     if (T == 0) {                                                 // window 0: the frame is only a neighbour, pass it through
         if (sp == 0)
@@ -78,7 +103,7 @@ __global__ void __launch_bounds__(kNlmThreads, 2) nlm_kernel(const NlmArgs a)
         return;
     }
 
-    // words of the frame being denoised that this thread's pass-A tasks compare against (offset independent)
+    // words of the frame being denoised that this thread's horizontal-pass tasks compare against (offset independent)
     uint32_t i0[ROUNDS][NW];
 #pragma unroll
     for (int rd = 0; rd < ROUNDS; ++rd) {
@@ -95,23 +120,98 @@ __global__ void __launch_bounds__(kNlmThreads, 2) nlm_kernel(const NlmArgs a)
         }
     }
 
-    int est[K], wsum[K];
+    int est[K], wsum[K];                                        // [2 * i + column] of the thread's K/2 rows x 2 columns
 #pragma unroll
     for (int i = 0; i < K; ++i) est[i] = wsum[i] = 0;
 
     const int rows_all = T * sws;
     const int per = (rows_all + a.nsplit - 1) / a.nsplit;
     const int row_lo = sp * per, row_hi = min(rows_all, row_lo + per);
-    const int j = tid & (TW - 1), rh = tid / TW;
-    int cur_t = -1;
+    // vertical pass: a thread owns two adjacent columns (one 64-bit shared load serves both) and K/2 rows
+    constexpr int KB = K / 2;
+    const int j = (tid & (TW / 2 - 1)) * 2, rh = tid / (TW / 2);
+    if (LS) {
+        for (int i = tid; i <= lut_n; i += kNlmThreads) s_lut[i] = (unsigned short)lut[i];
+        // visible after the first __syncthreads below (the region staging)
+    }
 
+    // ---- horizontal pass of one offset into buffer `buf`: TWS-wide sums of squared differences
+    auto pass_a = [&](int dy, int dx, int buf) {
+        int *s_h = s_h0 + buf * (NR * HP);
+#pragma unroll
+        for (int rd = 0; rd < ROUNDS; ++rd) {
+            const int task = tid + rd * kNlmThreads;
+            if (task < NTASK) {
+                const int seg = task / NR, r = task - seg * NR;
+                const int start = seg * S + dx + sh;
+                const uint32_t *row = reinterpret_cast<const uint32_t *>(s_it + (r + sh + dy) * itp) + (start >> 2);
+                const int sft = (start & 3) * 8;
+                uint32_t w[NW + 1], d[NW];
+#pragma unroll
+                for (int k = 0; k <= NW; ++k) w[k] = row[k];
+#pragma unroll
+                for (int k = 0; k < NW; ++k) d[k] = __vabsdiffu4(i0[rd][k], __funnelshift_r(w[k], w[k + 1], sft));
+                int px[NPX];
+#pragma unroll
+                for (int x = 0; x < NPX; ++x) px[x] = (int)__byte_perm(d[x >> 2], 0u, 0x4440u | (unsigned)(x & 3));   // one PRMT per pixel
+                int sum = 0;
+#pragma unroll
+                for (int x = 0; x < TWS; ++x) sum += px[x] * px[x];
+                int out[S];
+                out[0] = sum;
+#pragma unroll
+                for (int c = 1; c < S; ++c) {
+                    sum += px[c + TWS - 1] * px[c + TWS - 1];
+                    sum -= px[c - 1] * px[c - 1];
+                    out[c] = sum;
+                }
+                int4 *dstp = reinterpret_cast<int4 *>(s_h + r * HP + seg * S);
+#pragma unroll
+                for (int e = 0; e < S / 4; ++e) dstp[e] = make_int4(out[4 * e], out[4 * e + 1], out[4 * e + 2], out[4 * e + 3]);
+            }
+        }
+    };
+    // ---- vertical pass of one offset from buffer `buf`: TWS-high sums, weights, accumulation
+    auto pass_b = [&](int dy, int dx, int buf) {
+        const int *hp = s_h0 + buf * (NR * HP) + (rh * KB) * HP + j;
+        const unsigned char *pp = s_it + (rh * KB + b + dy) * itp + (j + b + dx);
+        int v0 = 0, v1 = 0;
+#pragma unroll
+        for (int r = 0; r < TWS; ++r) {
+            const int2 h2 = *reinterpret_cast<const int2 *>(hp + r * HP);
+            v0 += h2.x; v1 += h2.y;
+        }
+#pragma unroll
+        for (int i = 0; i < KB; ++i) {
+            int w0, w1;
+            if (LS) {
+                w0 = s_lut[min(v0 >> SHIFT, lut_n)];                 // clamped: the entry after the table is 0
+                w1 = s_lut[min(v1 >> SHIFT, lut_n)];
+            } else {
+                w0 = __ldg(lut + min(v0 >> SHIFT, lut_n));
+                w1 = __ldg(lut + min(v1 >> SHIFT, lut_n));
+            }
+            est[2 * i] += w0 * (int)pp[i * itp];
+            est[2 * i + 1] += w1 * (int)pp[i * itp + 1];
+            wsum[2 * i] += w0;
+            wsum[2 * i + 1] += w1;
+            if (i + 1 < KB) {
+                const int2 in = *reinterpret_cast<const int2 *>(hp + (i + TWS) * HP), out = *reinterpret_cast<const int2 *>(hp + i * HP);
+                v0 += in.x - out.x; v1 += in.y - out.y;
+            }
+        }
+    };
+
+    int cur_t = -1, pend_dy = 0, pend_dx = 0, buf = 0;
+    bool pending = false;
     for (int orow = row_lo; orow < row_hi; ++orow) {
         const int ti = orow / sws, dy = orow - ti * sws - sh;
         if (ti != cur_t) {                                        // stage the next temporal frame's region
             cur_t = ti;
+            if (pending) { pass_b(pend_dy, pend_dx, buf ^ 1); pending = false; }    // the last offset of the old frame still reads the old region
             const uint8_t *f = main_f + (long long)(ti - half) * a.frame_stride;
             __syncthreads();
-            for (int idx = tid; idx < a.it_rows * itw; idx += kNlmThreads) {
+            for (int idx = tid; idx < it_rows * itw; idx += kNlmThreads) {
                 const int rr = idx / itw, wc = idx - rr * itw;
                 const uint8_t *row = f + (size_t)reflect101_iter(y0 - b + rr, a.H) * a.pitch;
                 uint32_t w = 0;
@@ -122,67 +222,19 @@ __global__ void __launch_bounds__(kNlmThreads, 2) nlm_kernel(const NlmArgs a)
             __syncthreads();
         }
         for (int dx = -sh; dx <= sh; ++dx) {
-            // ---- pass A: horizontal TWS-sums of squared differences
-#pragma unroll
-            for (int rd = 0; rd < ROUNDS; ++rd) {
-                const int task = tid + rd * kNlmThreads;
-                if (task < NTASK) {
-                    const int seg = task / NR, r = task - seg * NR;
-                    const int start = seg * S + dx + sh;
-                    const uint32_t *row = reinterpret_cast<const uint32_t *>(s_it + (r + sh + dy) * a.itp) + (start >> 2);
-                    const int sft = (start & 3) * 8;
-                    uint32_t w[NW + 1], d[NW];
-#pragma unroll
-                    for (int k = 0; k <= NW; ++k) w[k] = row[k];
-#pragma unroll
-                    for (int k = 0; k < NW; ++k) d[k] = __vabsdiffu4(i0[rd][k], __funnelshift_r(w[k], w[k + 1], sft));
-                    int px[NPX];
-#pragma unroll
-                    for (int x = 0; x < NPX; ++x) px[x] = (int)__byte_perm(d[x >> 2], 0u, 0x4440u | (unsigned)(x & 3));   // one PRMT per pixel
-                    int sum = 0;
-#pragma unroll
-                    for (int x = 0; x < TWS; ++x) sum += px[x] * px[x];
-                    int out[S];
-                    out[0] = sum;
-#pragma unroll
-                    for (int c = 1; c < S; ++c) {
-                        sum += px[c + TWS - 1] * px[c + TWS - 1];
-                        sum -= px[c - 1] * px[c - 1];
-                        out[c] = sum;
-                    }
-                    int4 *dstp = reinterpret_cast<int4 *>(s_h + r * HP + seg * S);
-#pragma unroll
-                    for (int e = 0; e < S / 4; ++e) dstp[e] = make_int4(out[4 * e], out[4 * e + 1], out[4 * e + 2], out[4 * e + 3]);
-                }
-            }
+            pass_a(dy, dx, buf);
+            if (pending) pass_b(pend_dy, pend_dx, buf ^ 1);
             __syncthreads();
-            // ---- pass B: vertical TWS-sums, weights, accumulation
-            {
-                const int *hp = s_h + (rh * K) * HP + j;
-                const unsigned char *pp = s_it + (rh * K + b + dy) * a.itp + (j + b + dx);
-                int v = 0;
-#pragma unroll
-                for (int r = 0; r < TWS; ++r) v += hp[r * HP];
-#pragma unroll
-                for (int i = 0; i < K; ++i) {
-                    const int ad = v >> a.shift;
-                    int wgt = 0;
-                    if (ad < lut_n) wgt = __ldg(lut + ad);            // one predicated load, no divergent region
-                    est[i] += wgt * (int)pp[i * a.itp];
-                    wsum[i] += wgt;
-                    if (i + 1 < K) v += hp[(i + TWS) * HP] - hp[i * HP];
-                }
-            }
-            __syncthreads();
+            pend_dy = dy; pend_dx = dx; pending = true;
+            buf ^= 1;
         }
     }
+    if (pending) pass_b(pend_dy, pend_dx, buf ^ 1);
 
-    const int gx = x0 + j;
-    if (gx >= a.W) return;
 #pragma unroll
     for (int i = 0; i < K; ++i) {
-        const int gy = y0 + rh * K + i;
-        if (gy >= a.H) break;
+        const int gy = y0 + rh * KB + (i >> 1), gx = x0 + j + (i & 1);
+        if (gy >= a.H || gx >= a.W) continue;
         if (a.nsplit > 1) {
             int *acc = a.acc + (((long long)n * a.H + gy) * a.W + gx) * 2;
             if (wsum[i]) { atomicAdd(acc, est[i]); atomicAdd(acc + 1, wsum[i]); }
