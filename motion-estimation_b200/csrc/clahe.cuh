@@ -6,10 +6,12 @@
 //   clahe_lut_kernel    one CTA per (tile, frame): 256-bin histogram in shared memory (reflect-101
 //                       extension when the frame does not divide into the tile grid), clip, batch +
 //                       strided-residual redistribution, inclusive scan, LUT = round(cumsum * 255 / area)
-//   clahe_apply_kernel  4 pixels per thread: bilinear blend of the four surrounding tile LUTs in binary32
-//                       with OpenCV's operation order (no FMA contraction), one rounding, in place.
+//   clahe_pack_kernel   the four tables of every interpolation cell packed into one word per grey level
+//   clahe_apply_kernel  bilinear blend of the four surrounding tile LUTs in binary32 with OpenCV's operation
+//                       order (no FMA contraction), one rounding, in place; one table word per pixel.
 // Both are HBM-bound streaming kernels: 3 bytes of traffic per pixel (read, read, write) + 16 KB of LUTs per frame.
 #pragma once
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -35,7 +37,9 @@ __device__ __forceinline__ int reflect101(int i, int n)
 
 __global__ void __launch_bounds__(256) clahe_lut_kernel(const ClaheArgs a, int first_slot)
 {
-    __shared__ unsigned whist[8][256];                   // one histogram per warp: an eighth of the atomic contention
+    // one histogram per warp: an eighth of the atomic contention (four copies per warp, by lane quarter, were tried and lost:
+    // 68 -> 80 us, r02h -- the extra clearing and summing costs more than the same-address atomics it avoids)
+    __shared__ unsigned whist[8][256];
     __shared__ unsigned wsum[8];
     __shared__ unsigned s_clipped;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -47,16 +51,40 @@ __global__ void __launch_bounds__(256) clahe_lut_kernel(const ClaheArgs a, int f
     __syncthreads();
     const int xb = ti * a.tw, xe = xb + a.tw;             // the tile's columns; beyond W only in the reflect-extended case
     if (xe <= a.W) {
-        // one warp per row, four pixels per load: aligned words that cover [xb, xe), bytes outside it masked off
-        const int w0 = xb >> 2, w1 = (xe + 3) >> 2;
-        for (int r = warp; r < a.th; r += 8) {
-            const uint32_t *row = reinterpret_cast<const uint32_t *>(f + (size_t)reflect101(tj * a.th + r, a.H) * a.pitch);
-            for (int w = w0 + lane; w < w1; w += 32) {
-                const uint32_t v = __ldg(row + w);
+        // four pixels per load: aligned words that cover [xb, xe), bytes outside it masked off.  The tile's (row, word) pairs
+        // are spread over the whole CTA and four loads are in flight per thread before the first histogram update (r02a ncu
+        // of the one-row-per-warp form: 8.5 long-scoreboard stalls per issued instruction, 1.5 TB/s).
+        const int w0 = xb >> 2, w1 = (xe + 3) >> 2, nw = w1 - w0, total = a.th * nw;
+        const unsigned magic = nw > 1 ? (unsigned)(0x100000000ull / (unsigned)nw + 1ull) : 0u;
+        for (int p0 = tid; p0 < total; p0 += 4 * 256) {
+            uint32_t v[4];
+            int wi[4];
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const int x = 4 * w + q;
-                    if (x >= xb && x < xe) atomicAdd(&whist[warp][(v >> (8 * q)) & 255u], 1u);
+            for (int u = 0; u < 4; ++u) {
+                const int p = p0 + u * 256;
+                wi[u] = -1;
+                if (p < total) {
+                    const int r = magic ? (int)__umulhi((unsigned)p, magic) : p;
+                    wi[u] = w0 + p - r * nw;
+                    v[u] = __ldg(reinterpret_cast<const uint32_t *>(f + (size_t)reflect101(tj * a.th + r, a.H) * a.pitch) + wi[u]);
+                }
+            }
+            if (((xb | xe) & 3) == 0) {                      // tile edges on word boundaries (the usual case): no per-byte tests
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (wi[u] < 0) continue;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) atomicAdd(&whist[warp][(v[u] >> (8 * q)) & 255u], 1u);
+                }
+            } else {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (wi[u] < 0) continue;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int x = 4 * wi[u] + q;
+                        if (x >= xb && x < xe) atomicAdd(&whist[warp][(v[u] >> (8 * q)) & 255u], 1u);
+                    }
                 }
             }
         }
@@ -102,60 +130,111 @@ __global__ void __launch_bounds__(256) clahe_lut_kernel(const ClaheArgs a, int f
     a.luts[((size_t)(frame * a.ty + tj) * a.tx + ti) * 256 + tid] = (uint8_t)q;
 }
 
-// Rows per CTA of clahe_apply_kernel and the largest tile grid whose lookup tables it keeps in shared memory.
-constexpr int kClaheRows = 8, kClaheSmemTiles = 64;
-
-// One CTA = kClaheRows rows of one frame, 16 pixels (one 16-byte load and store) per thread and step.  The frame's
-// lookup tables (16 KB for the 8x8 grid) are staged in shared memory once per CTA, so the four table reads per pixel
-// are shared-memory byte loads instead of scattered global ones (r01: the global form ran at 0.75 TB/s).
-__global__ void __launch_bounds__(256) clahe_apply_kernel(const ClaheArgs a, int first_slot)
+// ---------------------------------------------------------------- packed interpolation tables
+// A pixel blends the tables of the four tiles around it.  All pixels of one interpolation CELL (the rectangle between
+// four tile centres; (tx + 1) x (ty + 1) cells per frame) use the same four tables, so those are packed once per frame
+// into one 8-byte entry per grey level: (top-left, top-right, bottom-left, bottom-right) as binary16.  The apply kernel then
+// makes ONE 64-bit lookup per pixel instead of four byte lookups and four integer conversions (r02a ncu of the byte form: 49 M
+// shared wavefronts, 31 M of them bank conflicts, 48 thread-instructions per pixel).
+__global__ void __launch_bounds__(256) clahe_pack_kernel(const ClaheArgs a, uint2 *packed)
 {
-    __shared__ __align__(16) uint8_t s_lut[kClaheSmemTiles * 256];
+    const int cells_x = a.tx + 1, cy = blockIdx.x / cells_x, cx = blockIdx.x - cy * cells_x, frame = blockIdx.y, v = threadIdx.x;
+    const int tx1 = max(cx - 1, 0), tx2 = min(cx, a.tx - 1), ty1 = max(cy - 1, 0), ty2 = min(cy, a.ty - 1);
+    const uint8_t *l = a.luts + (size_t)frame * a.ty * a.tx * 256;
+    // as binary16 (0..255 are exact): half -> float is one full-rate instruction in the apply kernel, where byte -> float costs
+    // either the 16-lane conversion unit or a PRMT on the ALU pipe that kernel is bound by; 16-byte binary32 entries were tried
+    // and lost (r02f: 185 us against 155 us, four-bank lookups and a 72 KB table to stage per CTA)
+    const __half2 top = __floats2half2_rn((float)l[(ty1 * a.tx + tx1) * 256 + v], (float)l[(ty1 * a.tx + tx2) * 256 + v]);
+    const __half2 bot = __floats2half2_rn((float)l[(ty2 * a.tx + tx1) * 256 + v], (float)l[(ty2 * a.tx + tx2) * 256 + v]);
+    packed[((size_t)frame * (a.ty + 1) * cells_x + blockIdx.x) * 256 + v] =
+        make_uint2(*reinterpret_cast<const unsigned *>(&top), *reinterpret_cast<const unsigned *>(&bot));
+}
+
+// Rows per CTA of clahe_apply_kernel; the packed tables of the (at most two) cell rows those image rows touch are staged
+// in shared memory when they fit (kClaheSmemCells cells; the reference's 8x8 grid needs 2 x 9).
+constexpr int kClaheRows = 16, kClaheSmemCells = 20;
+
+// One CTA = kClaheRows rows of one frame.  A thread owns one 4-pixel word column at a time and walks the rows: the
+// x-dependent interpolation terms (OpenCV computes them per column: cell index, xa, 1 - xa) are computed once per word
+// column, the y-dependent ones once per row and CTA, and a pixel costs one table word, four conversions, nine binary32
+// operations in OpenCV's order (no FMA contraction) and one rounding.
+__global__ void __launch_bounds__(256) clahe_apply_kernel(const ClaheArgs a, int first_slot, const uint2 *__restrict__ packed)
+{
+    __shared__ __align__(16) uint2 s_tab[kClaheSmemCells * 256];                        // 40 KB
+    __shared__ float s_ya[kClaheRows], s_ya1[kClaheRows];
+    __shared__ int s_cy[kClaheRows];
     const int frame = blockIdx.y, y_lo = blockIdx.x * kClaheRows, tid = threadIdx.x;
+    const int cells_x = a.tx + 1;
     uint8_t *fbase = a.frames + (long long)(first_slot + frame) * a.frame_stride;
-    const uint8_t *glut = a.luts + (size_t)frame * a.ty * a.tx * 256;
-    const int ntile = a.tx * a.ty;
-    const uint8_t *lut = glut;
-    if (ntile <= kClaheSmemTiles) {
-        const uint4 *src = reinterpret_cast<const uint4 *>(glut);
-        for (int i = tid; i < ntile * 16; i += 256) reinterpret_cast<uint4 *>(s_lut)[i] = __ldg(src + i);
+    const uint2 *gtab = packed + (size_t)frame * (a.ty + 1) * cells_x * 256;
+    const int rows = min(kClaheRows, a.H - y_lo);
+    if (tid < rows) {
+        const float tyf = __fsub_rn(__fmul_rn((float)(y_lo + tid), a.inv_th), 0.5f);
+        const int t1 = (int)floorf(tyf);
+        const float ya = __fsub_rn(tyf, (float)t1);
+        s_ya[tid] = ya; s_ya1[tid] = __fsub_rn(1.0f, ya); s_cy[tid] = t1 + 1;          // cell row 0 .. ty
+    }
+    __syncthreads();
+    const int cy_lo = s_cy[0], n_cy = s_cy[rows - 1] - cy_lo + 1;                       // 1 or 2 cell rows (more only for tiles under 8 rows)
+    const bool staged = n_cy * cells_x <= kClaheSmemCells;
+    if (staged) {
+        const uint4 *src = reinterpret_cast<const uint4 *>(gtab + (size_t)cy_lo * cells_x * 256);
+        for (int i = tid; i < n_cy * cells_x * 128; i += 256) reinterpret_cast<uint4 *>(s_tab)[i] = __ldg(src + i);
         __syncthreads();
-        lut = s_lut;
     }
-    const int chunks = (a.W + 15) >> 4;                                   // 16-pixel chunks per row
-    for (int it = tid; it < kClaheRows * chunks; it += 256) {
-        const int ry = it / chunks, cx = it - ry * chunks, y = y_lo + ry, x16 = cx << 4;
-        if (y >= a.H) break;
-        uint8_t *row = fbase + (size_t)y * a.pitch;
-        const float tyf = __fsub_rn(__fmul_rn((float)y, a.inv_th), 0.5f);
-        int ty1 = (int)floorf(tyf);
-        const float ya = __fsub_rn(tyf, (float)ty1), ya1 = __fsub_rn(1.0f, ya);
-        const int ty2 = min(ty1 + 1, a.ty - 1);
-        ty1 = max(ty1, 0);
-        const uint8_t *l1 = lut + (size_t)ty1 * a.tx * 256, *l2 = lut + (size_t)ty2 * a.tx * 256;
-        // one pixel: bilinear blend of the four surrounding tables, OpenCV's operation order, one rounding
-        auto pixel = [&](int x, int v) {
-            const float txf = __fsub_rn(__fmul_rn((float)x, a.inv_tw), 0.5f);
-            int tx1 = (int)floorf(txf);
-            const float xa = __fsub_rn(txf, (float)tx1), xa1 = __fsub_rn(1.0f, xa);
-            const int tx2 = min(tx1 + 1, a.tx - 1);
-            tx1 = max(tx1, 0);
-            const float top = __fadd_rn(__fmul_rn((float)l1[tx1 * 256 + v], xa1), __fmul_rn((float)l1[tx2 * 256 + v], xa));
-            const float bot = __fadd_rn(__fmul_rn((float)l2[tx1 * 256 + v], xa1), __fmul_rn((float)l2[tx2 * 256 + v], xa));
-            const int q = __float2int_rn(__fadd_rn(__fmul_rn(top, ya1), __fmul_rn(bot, ya)));
-            return (uint32_t)(q < 0 ? 0 : (q > 255 ? 255 : q));
-        };
-        if (x16 + 16 <= a.W) {
-            const uint4 v = *reinterpret_cast<const uint4 *>(row + x16);
-            const uint32_t in[4] = {v.x, v.y, v.z, v.w};
-            uint32_t out[4] = {0, 0, 0, 0};
+    // The blend in binary32, OpenCV's operation order (no FMA contraction).  The result becomes a byte without the conversion
+    // unit (16 lanes per clock and SM; the I2F / F2I form was bound by it: r02b, 191 us per 64 frames): adding 1.5 * 2^23 rounds
+    // to the nearest even integer exactly as cvRound / __float2int_rn does and leaves it in the low mantissa bits.  0 <= v <
+    // 255.5 by construction (table entries are 0..255, xa + (1 - xa) <= 1 + 2^-24), so no clamp is needed.
+    auto blend = [](uint2 t, float xa, float xa1, float ya, float ya1) {
+        const float2 tt = __half22float2(*reinterpret_cast<const __half2 *>(&t.x)), tb = __half22float2(*reinterpret_cast<const __half2 *>(&t.y));
+        const float top = __fadd_rn(__fmul_rn(tt.x, xa1), __fmul_rn(tt.y, xa));
+        const float bot = __fadd_rn(__fmul_rn(tb.x, xa1), __fmul_rn(tb.y, xa));
+        const float v = __fadd_rn(__fmul_rn(top, ya1), __fmul_rn(bot, ya));
+        return __float_as_uint(__fadd_rn(v, 12582912.0f)) - 0x4B400000u;
+    };
+    // the same loop twice, so that the staged form reads the table with shared-memory loads (a pointer chosen at run time
+    // compiles to generic loads): `tab` is indexed [(cy - cy_lo) * cells_x + cx][v]
+    auto run = [&](const uint2 *tab) {
+        const int words = a.W >> 2;
+        for (int cw = tid; cw < words; cw += 256) {
+            float xa[4], xa1[4];
+            int cell[4];
 #pragma unroll
-            for (int i = 0; i < 16; ++i) out[i >> 2] |= pixel(x16 + i, (int)((in[i >> 2] >> (8 * (i & 3))) & 255u)) << (8 * (i & 3));
-            *reinterpret_cast<uint4 *>(row + x16) = make_uint4(out[0], out[1], out[2], out[3]);
-        } else {
-            for (int x = x16; x < a.W; ++x) row[x] = (uint8_t)pixel(x, row[x]);
+            for (int i = 0; i < 4; ++i) {
+                const float txf = __fsub_rn(__fmul_rn((float)(4 * cw + i), a.inv_tw), 0.5f);
+                const int t1 = (int)floorf(txf);
+                xa[i] = __fsub_rn(txf, (float)t1); xa1[i] = __fsub_rn(1.0f, xa[i]);
+                cell[i] = (t1 + 1) * 256;
+            }
+            uint32_t in[kClaheRows];                             // all rows' words in flight before the first one is needed
+            uint32_t *p0 = reinterpret_cast<uint32_t *>(fbase + (size_t)y_lo * a.pitch) + cw;
+#pragma unroll
+            for (int r = 0; r < kClaheRows; ++r)
+                if (r < rows) in[r] = *reinterpret_cast<const uint32_t *>(reinterpret_cast<const uint8_t *>(p0) + (size_t)r * a.pitch);
+#pragma unroll
+            for (int r = 0; r < kClaheRows; ++r) {
+                if (r >= rows) break;
+                const float ya = s_ya[r], ya1 = s_ya1[r];
+                const uint2 *trow = tab + (size_t)(s_cy[r] - cy_lo) * cells_x * 256;
+                uint32_t out = 0;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) out |= blend(trow[cell[i] + ((in[r] >> (8 * i)) & 255u)], xa[i], xa1[i], ya, ya1) << (8 * i);
+                *reinterpret_cast<uint32_t *>(reinterpret_cast<uint8_t *>(p0) + (size_t)r * a.pitch) = out;
+            }
         }
-    }
+        for (int x = 4 * words + (tid & 3); x < a.W && tid < 4 * rows; x += 4) {       // ragged right edge (W not a multiple of 4)
+            const int r = tid >> 2;
+            const float txf = __fsub_rn(__fmul_rn((float)x, a.inv_tw), 0.5f);
+            const int t1 = (int)floorf(txf);
+            const float xa = __fsub_rn(txf, (float)t1);
+            uint8_t *px = fbase + (size_t)(y_lo + r) * a.pitch + x;
+            const uint2 *trow = tab + (size_t)(s_cy[r] - cy_lo) * cells_x * 256;
+            *px = (uint8_t)blend(trow[(t1 + 1) * 256 + *px], xa, __fsub_rn(1.0f, xa), s_ya[r], s_ya1[r]);
+        }
+    };
+    if (staged) run(s_tab);
+    else run(gtab + (size_t)cy_lo * cells_x * 256);
 }
 
 } // namespace me

@@ -120,7 +120,9 @@ int raise_smem_limit(const void *fn, bool prefer_smem = true)
     CU_TRY(cudaGetDevice(&dev));
     std::lock_guard<std::mutex> lock(mu);
     if (done.count({fn, dev})) return ME_OK;
-    CU_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemOptInMax));
+    cudaFuncAttributes fa;
+    CU_TRY(cudaFuncGetAttributes(&fa, fn));          // static shared memory counts against the same 227 KB
+    CU_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemOptInMax - (int)fa.sharedSizeBytes));
     if (prefer_smem) CU_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     done.insert({fn, dev});
     return ME_OK;
@@ -794,7 +796,10 @@ int me_clahe(me_ctx *c, int first_slot, int n_frames, double clip_limit, int til
     a.clip = 0;
     if (clip_limit > 0) { a.clip = (int)(clip_limit * area / 256); if (a.clip < 1) a.clip = 1; }
     a.inv_tw = 1.0f / (float)a.tw; a.inv_th = 1.0f / (float)a.th;
-    const size_t need = (size_t)c->max_frames * tiles_x * tiles_y * 256;
+    // Tables live only between the kernels of one chunk of frames: per frame 256 B per tile + 2 KB per interpolation cell.
+    const int chunk = n_frames < 64 ? n_frames : 64;
+    const size_t lut_bytes = (size_t)chunk * tiles_x * tiles_y * 256;
+    const size_t need = align_up(lut_bytes, 256) + (size_t)chunk * (tiles_x + 1) * (tiles_y + 1) * 2048;
     if (c->d_luts_bytes < need) {
         CU_TRY(cudaStreamSynchronize(c->s_copy));
         if (c->d_luts) CU_TRY(cudaFree(c->d_luts));
@@ -803,13 +808,19 @@ int me_clahe(me_ctx *c, int first_slot, int n_frames, double clip_limit, int til
         c->d_luts_bytes = need;
     }
     a.luts = c->d_luts;
+    uint2 *packed = reinterpret_cast<uint2 *>(c->d_luts + align_up(lut_bytes, 256));
     for (auto &r : c->recent)                        // the frames are rewritten in place: wait for searches that read them
         if (r.used && r.lo < first_slot + n_frames && r.hi >= first_slot) CU_TRY(cudaStreamWaitEvent(c->s_copy, r.done, 0));
-    me::clahe_lut_kernel<<<dim3((unsigned)(tiles_x * tiles_y), (unsigned)n_frames), 256, 0, c->s_copy>>>(a, first_slot);
-    CU_TRY(cudaGetLastError());
-    me::clahe_apply_kernel<<<dim3((unsigned)ceil_div(c->H, me::kClaheRows), (unsigned)n_frames), 256, 0, c->s_copy>>>(a, first_slot);
-    CU_TRY(cudaGetLastError());
-    c->launches += 2;
+    for (int f = 0; f < n_frames; f += chunk) {
+        const int nf = n_frames - f < chunk ? n_frames - f : chunk;
+        me::clahe_lut_kernel<<<dim3((unsigned)(tiles_x * tiles_y), (unsigned)nf), 256, 0, c->s_copy>>>(a, first_slot + f);
+        CU_TRY(cudaGetLastError());
+        me::clahe_pack_kernel<<<dim3((unsigned)((tiles_x + 1) * (tiles_y + 1)), (unsigned)nf), 256, 0, c->s_copy>>>(a, packed);
+        CU_TRY(cudaGetLastError());
+        me::clahe_apply_kernel<<<dim3((unsigned)ceil_div(c->H, me::kClaheRows), (unsigned)nf), 256, 0, c->s_copy>>>(a, first_slot + f, packed);
+        CU_TRY(cudaGetLastError());
+        c->launches += 3;
+    }
     CU_TRY(cudaEventRecord(c->ev_upload, c->s_copy));   // same stream as the uploads: ordered after them, searches wait for this event
     c->have_upload = true;
     return ME_OK;
