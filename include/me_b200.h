@@ -236,8 +236,10 @@ int me_microbench_vabsdiff4(int device, int mode, double *instr_per_clk_per_sm, 
  * All calls share that array and it keeps the previous call's contents; what must be zero is
  * cleared on `stream` before each launch.  Calls whose kernels could overlap on the GPU race on it:
  * keep them on one stream or order them.  The first call on a device also performs that device's
- * one-time set-up and should be made outside stream capture.  Asynchronous: d_out is valid once
- * `stream` has drained.  Neither cudaMalloc/cudaFree nor any allocating library routine is called. */
+ * one-time set-up (thread-safe) and should be made outside stream capture.  Asynchronous: d_out is
+ * valid once `stream` has drained -- provided `pairs` is page-locked host memory that stays untouched
+ * until then; a pageable `pairs` is staged by the CUDA runtime, which makes the call wait for the
+ * stream first.  Neither cudaMalloc/cudaFree nor any allocating library routine is called. */
 #define ME_STATIC_SCRATCH_BYTES (4u << 20)
 int me_search_static_scratch(const uint8_t *d_frames, size_t pitch, int n_frames, int height, int width,
                              const me_params *params, const int32_t *pairs, int n_pairs,

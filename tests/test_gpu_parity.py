@@ -313,6 +313,27 @@ def test_rectangular_range_equals_oracle(me, monkeypatch, H, W, B, R, Ry, mode):
         assert one[0].tobytes() == res[3].tobytes()
 
 
+def test_resident_search_overlapping_denoise_on_the_copy_stream(me):
+    """Pre-processing kernels run on the copy stream while a resident (one CTA per SM) search runs on the compute stream:
+    NLM CTAs hold SMs, so not all resident CTAs need to be co-resident from the start.  Results and the kernel's error flag
+    must be unaffected (fetch_pairs raises if the resident kernel's wait guard tripped)."""
+    from motion_estimation_b200 import synth
+    H, W, n = 360, 640, 8
+    frames, shifts = synth.translating_frames(n + 12, H, W, 24, seed_texture=41, seed_motion=42)
+    cfg = me.SearchConfig(block=16, range=32)
+    with me.MotionEstimator(H, W, cfg, max_frames=n + 12, max_pairs=n) as est:
+        assert est.geometry["resident_kernel"] == 1
+        est.upload(frames)
+        pairs = [(k, k + 1) for k in range(n)]
+        want = est.search(pairs).copy()
+        for rep in range(3):
+            est.launch(pairs)                                             # compute stream: resident kernel over slots 0..n
+            est.denoise(n + 1, [1] * 11, 15.0, 19, 41)                    # copy stream: NLM on slots the search does not read
+            got = est.fetch_pairs(n)
+            assert got.tobytes() == want.tobytes(), rep
+        check_pair(est, 2, frames[2], frames[3], cfg, got[2])
+
+
 def _noisy_translating_frames(n, H, W, max_shift, seed):
     """Translating texture plus independent per-frame noise: the SAD minima are not exact zeros, so the sub-pixel fit,
     the peak gates and the median all have real work to do."""

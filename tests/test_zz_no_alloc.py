@@ -52,6 +52,36 @@ def test_static_scratch_entry_point_equals_context_entry_point(me):
             assert want["flag"].all() and want["nvalid_x"].min() > 10
 
 
+def test_static_scratch_against_the_oracle_and_without_allocating(me):
+    """The entry point checked directly against the CPU oracle (not only against the context path), and its promise checked
+    too: free device memory as the driver reports it (cudaMemGetInfo) is the same before and after a call that follows the
+    first one -- the first call may still load the kernel module, later ones must not touch the allocator at all."""
+    import torch
+    from motion_estimation_b200 import synth
+    from oracle import sad as osad
+    H, W = 128, 320
+    cfg = me.SearchConfig(block=16, range=24, range_y=6)
+    stream = torch.cuda.current_stream().cuda_stream
+    frames, _ = synth.translating_frames(3, H, W, 10, seed_texture=5, seed_motion=6)
+    t = torch.from_numpy(frames).cuda().contiguous()
+    pairs = [(0, 1), (1, 2), (2, 0)]
+    out = torch.zeros(len(pairs) * 8, dtype=torch.int32, device="cuda")
+    assert _static_search(me, t, pairs, cfg, out, stream) == 0, me._lib.lib().me_last_error()       # first call: one-time set-up
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    for _ in range(2):
+        assert _static_search(me, t, pairs, cfg, out, stream) == 0, me._lib.lib().me_last_error()
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free1 == free0, f"device memory changed by {free0 - free1} bytes across calls that must not allocate"
+    got = out.cpu().numpy().view(me.PAIR_DTYPE)
+    for i, (a, b) in enumerate(pairs):
+        o = osad.search(frames[a], frames[b], 16, 24, range_y=6)
+        assert (got[i]["pdx"], got[i]["pdy"], got[i]["flag"], got[i]["nvalid_x"], got[i]["nvalid_y"], got[i]["n_textured"],
+                got[i]["mean_dx"], got[i]["mean_dy"]) == (o["pdx"], o["pdy"], o["flag"], o["nvalid_x"], o["nvalid_y"],
+                                                          o["n_textured"], o["mean_dx"], o["mean_dy"]), i
+
+
 def test_static_scratch_with_candidate_slabs(me):
     """A range large enough to be cut into several CTAs per tile uses two more pieces of the shared array."""
     import torch
