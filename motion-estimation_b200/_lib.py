@@ -57,7 +57,7 @@ BUILD_DIR = os.path.join(_HERE, "build")
 
 
 def sources():
-    names = ("me_api.cu", "search_inst.cu", "sad_search.cuh", "sad_persistent.cuh", "kernel_choice.h", "misc_kernels.cuh", "clahe.cuh", "nlm.cuh")
+    names = ("me_api.cu", "search_inst.cu", "sad_search.cuh", "sad_persistent.cuh", "sad_scan.cuh", "kernel_choice.h", "misc_kernels.cuh", "clahe.cuh", "nlm.cuh")
     return [os.path.join(_CSRC, n) for n in names] + [HEADER]
 
 

@@ -9,6 +9,7 @@ struct KernelChoice {
     const void *fn = nullptr;              // one CTA per tile, one block row per tile
     const void *fn_multirow = nullptr;     // the same kernel for tiles of several block rows
     const void *fn_persistent = nullptr;   // warp-specialised resident form
+    const void *fn_scan = nullptr;         // the anchored walk as one cooperative kernel (32-bit keys, one-row tiles only)
     int ndy = 0, nq = 0, maxt = 0, pitch = 0, rank_bits = 0, persist_threads = 0;
 };
 

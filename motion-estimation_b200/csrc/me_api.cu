@@ -20,6 +20,7 @@
 #include "../../include/me_b200.h"
 #include "sad_search.cuh"
 #include "sad_persistent.cuh"
+#include "sad_scan.cuh"
 #include "kernel_choice.h"
 #include "misc_kernels.cuh"
 #include "clahe.cuh"
@@ -187,6 +188,7 @@ struct me_ctx {
     int pstage_bytes = 0, smem_persistent = 0;    // resident kernel: one stage of window copies, total dynamic smem (0 = not usable)
     int *d_ready = nullptr, *d_error = nullptr;  // resident kernel: queue of completed pairs, wait-timeout flag
     size_t n_tile_tickets = 0;                    // entries of args.tile_ticket (slabbed plans only)
+    uint8_t *d_scan = nullptr;                    // me_anchored_scan on the device: [records max_frames | state 16 ints | barrier 2 words]
     int64_t launches = 0;
     int64_t cand_px = 0, cand_px_valid = 0;
 };
@@ -199,7 +201,11 @@ int configure(me_ctx *c)
     const int B = c->p.block, R = c->p.range, U = 2 * R + 1, W = c->W, H = c->H;
     const int MB = B < 16 ? 16 : B, NSUB = MB / B, NDY = kNDY, NQ = kNQ;
     me::SearchArgs &a = c->args;
-    const int Ry = (c->p.range_y > 0 && c->p.range_y < R) ? c->p.range_y : R, Uy = 2 * Ry + 1;
+    // vertical range: the caller's, and never more than H - B -- a larger |dy| leaves the frame for every block (the 64-pixel-tall
+    // recordings: +-48 of a +-64 square), so dropping those rows of the candidate square changes no result
+    int Ry = (c->p.range_y > 0 && c->p.range_y < R) ? c->p.range_y : R;
+    if (Ry > H - B && H - B >= 1) Ry = H - B;
+    const int Uy = 2 * Ry + 1;
     a.W = W; a.H = H; a.R = R; a.U = U;
     a.Ry = Ry; a.Uy = Uy; a.dy0 = R - Ry;
     a.nbx = W / B; a.nby = H / B; a.nb = a.nbx * a.nby;
@@ -725,7 +731,7 @@ int me_destroy(me_ctx *c)
     cudaFree(c->d_frames); cudaFree(c->d_bgr); cudaFree(c->d_luts); cudaFree(c->d_nlm); cudaFree(c->d_nlm_meta); cudaFree(c->d_pairs);
     cudaFree(c->args.blk_mv); cudaFree(c->args.blk_sad); cudaFree(c->args.blk_sub); cudaFree(c->args.blk_flags);
     cudaFree(c->args.pair_out); cudaFree(c->args.pair_ticket); cudaFree(c->args.blk_key); cudaFree(c->args.tile_ticket);
-    cudaFree(c->d_ready); cudaFree(c->d_error);
+    cudaFree(c->d_ready); cudaFree(c->d_error); cudaFree(c->d_scan);
     delete c->big;                                       // owns nothing: its pointers are the context's
     c->big = nullptr;
     for (int i = 0; i < 2; ++i) {
@@ -1072,6 +1078,71 @@ int me_estimate_pair(me_ctx *c, const uint8_t *prev, const uint8_t *cur, size_t 
     return rc;
 }
 
+} // extern "C"
+
+namespace {
+
+// The whole walk as one cooperative launch of sad_scan_kernel (sad_scan.cuh).  Returns ME_OK with *done = false when this
+// context's plan cannot use it (64-bit keys, multi-row tiles) -- the caller then drives the walk from the host.
+int anchored_scan_device(me_ctx *c, int anchor_slot, int first_slot, int n_frames, float scale, float gate,
+                         me_scan_record *out, int *searches, int *launches, bool *done)
+{
+    *done = false;
+    if (!c->kc.fn_scan || c->args.tmr != 1 || env_int("ME_SCAN_DEVICE", 1) == 0) return ME_OK;
+    int coop = 0;
+    CU_TRY(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->device));
+    if (!coop) return ME_OK;
+    cudaStream_t st = c->s_compute;
+    const size_t rec_bytes = align_up(sizeof(me_scan_record) * (size_t)c->max_frames, 256);
+    if (!c->d_scan) CU_TRY(cudaMalloc(&c->d_scan, rec_bytes + 256));
+    int rc = raise_smem_limit(c->kc.fn_scan);
+    if (rc) return rc;
+    int per_sm = 0;
+    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, c->kc.fn_scan, c->threads, (size_t)c->smem));
+    if (per_sm < 1) return ME_OK;
+    me::SearchArgs a = c->args;
+    a.frames = c->d_frames;
+    a.pairs = c->d_pairs;
+    me::ScanArgs sc;
+    sc.first_slot = first_slot; sc.n_frames = n_frames; sc.anchor_slot = anchor_slot;
+    sc.scale = scale; sc.gate = gate;
+    sc.max_look = c->max_pairs < 256 ? c->max_pairs : 256;
+    sc.out = reinterpret_cast<me_scan_record *>(c->d_scan);
+    sc.pairs = c->d_pairs;
+    sc.state = reinterpret_cast<int *>(c->d_scan + rec_bytes);
+    sc.sync = reinterpret_cast<unsigned *>(c->d_scan + rec_bytes + 64);
+    const long long most = (long long)a.tiles_per_pair * a.nsx * a.nsy * sc.max_look;      // units of the largest batch
+    // every CTA of the grid arrives at every barrier, with or without work: no more CTAs per SM than ME_SCAN_CTAS (tuned: see DESIGN.md 4)
+    const int cap = env_int("ME_SCAN_CTAS", 4);
+    if (cap > 0 && per_sm > cap) per_sm = cap;
+    long long grid = (long long)per_sm * c->sm_count;
+    if (grid > most) grid = most;
+    CU_TRY(cudaMemsetAsync(c->d_scan + rec_bytes, 0, 128, st));
+    void *params[4] = {(void *)&c->tm_win, (void *)&c->tm_ref, (void *)&a, (void *)&sc};
+    CU_TRY(cudaEventRecord(c->ev_k0, st));
+    CU_TRY(cudaLaunchCooperativeKernel(c->kc.fn_scan, dim3((unsigned)grid), dim3((unsigned)c->threads), params, (size_t)c->smem, st));
+    CU_TRY(cudaEventRecord(c->ev_k1, st));
+    c->launches += 1;
+    int state[8];
+    CU_TRY(cudaMemcpyAsync(state, sc.state, sizeof state, cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaMemcpyAsync(out, sc.out, sizeof(me_scan_record) * (size_t)n_frames, cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaStreamSynchronize(st));
+    c->have_search = true;
+    c->last_pairs = 1;
+    if (state[7]) {
+        report_search_timeout(c);
+        return fail(ME_ECUDA, "the resident scan kernel gave up waiting at a grid barrier; the context has been reset");
+    }
+    if (searches) *searches = state[5];
+    if (launches) *launches = state[6];
+    *done = true;
+    return ME_OK;
+}
+
+} // namespace
+
+extern "C" {
+
 int me_anchored_scan(me_ctx *c, int anchor_slot, int first_slot, int n_frames, float scale, float gate,
                      me_scan_record *out, int *searches, int *launches)
 {
@@ -1083,6 +1154,21 @@ int me_anchored_scan(me_ctx *c, int anchor_slot, int first_slot, int n_frames, f
     if (c->have_search) CU_TRY(cudaEventSynchronize(c->ev_search));   // h_pairs / h_pair_out are about to be reused
     if (c->have_upload) CU_TRY(cudaStreamWaitEvent(c->s_compute, c->ev_upload, 0));
     cudaStream_t st = c->s_compute;
+    {
+        bool done = false;
+        int rc = anchored_scan_device(c, anchor_slot, first_slot, n_frames, scale, gate, out, searches, launches, &done);
+        if (rc) return rc;
+        if (done) {
+            CU_TRY(cudaEventRecord(c->ev_search, st));
+            me_ctx::SearchRecord &r = c->recent[c->recent_next];
+            c->recent_next = (c->recent_next + 1) % 4;
+            r.lo = anchor_slot < first_slot ? anchor_slot : first_slot;
+            r.hi = anchor_slot > first_slot + n_frames - 1 ? anchor_slot : first_slot + n_frames - 1;
+            CU_TRY(cudaEventRecord(r.done, st));
+            r.used = true;
+            return ME_OK;
+        }
+    }
     int *h_err = reinterpret_cast<int *>(c->h_pair_out + c->max_pairs);
     const int end = first_slot + n_frames, max_look = c->max_pairs < 256 ? c->max_pairs : 256;
     int anchor = anchor_slot, k = first_slot, look = max_look < 4 ? max_look : 4, since = 0, n_search = 0, n_launch = 0, last = 0;

@@ -112,6 +112,10 @@ __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 }
+__device__ __forceinline__ void mbar_inval(uint64_t *bar)
+{
+    asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
 {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
@@ -770,20 +774,20 @@ __device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j
 // MR = tiles of several block rows (a.tmr > 1).  A separate instantiation: carrying the row arithmetic in the
 // one-row kernel cost it 3 % (r01e: 0.846 -> 0.819 at 1080p/16/+-32).
 constexpr bool kSliceMR = true;               // multi-row tiles (small ranges): 16-row patches as two rolled 8-row slices
-template <int B, int NDY, int NQ, int PITCH, bool K64, int RB, int MAXT, int MINB, bool MR>
-__global__ void __launch_bounds__(MAXT, MINB)
-sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_constant__ CUtensorMap tm_ref,
-                  const SearchArgs a)
+// search_tile: everything one CTA does for one unit (tile x candidate slab) -- the body of sad_search_kernel, and of every
+// iteration of sad_scan_kernel (sad_scan.cuh), which walks units in a loop.  `smem` is the CTA's dynamic shared memory.
+template <int B, int NDY, int NQ, int PITCH, bool K64, int RB, bool MR>
+__device__ __forceinline__ void search_tile(const CUtensorMap &tm_win, const CUtensorMap &tm_ref, const SearchArgs &a, const int unit,
+                                            uint8_t *smem)
 {
     using KeyT = typename KeyOf<K64>::T;
     using G = Geo<B>;
     constexpr KeyT kNone = ~KeyT(0);
     constexpr int LWW = (NQ % 4 == 0) ? 4 : 1;       // wide patches start on 16-byte boundaries when NQ % 4 == 0
-    extern __shared__ __align__(1024) uint8_t smem[];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
     const int nslab = a.nsx * a.nsy;
-    const int tile_id = blockIdx.x / nslab, slab = blockIdx.x - tile_id * nslab;   // slabs of a tile are adjacent CTAs
+    const int tile_id = unit / nslab, slab = unit - tile_id * nslab;               // slabs of a tile are adjacent units
     const int pair = tile_id / a.tiles_per_pair;
     const int tr = tile_id - pair * a.tiles_per_pair;
     const int ty = tr / a.tiles_x, tx = tr - ty * a.tiles_x;
@@ -791,7 +795,7 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     const int ubase = sx * a.su, dbase = a.dy0 + sy * a.sd;
     const int lastx = sx == a.nsx - 1;
     const int slab_w = lastx ? a.U - ubase : a.su, slab_h = (sy == a.nsy - 1) ? a.dy0 + a.Uy - dbase : a.sd;
-    const int prev_slot = __ldg(a.pairs + 2 * pair), cur_slot = __ldg(a.pairs + 2 * pair + 1);
+    const int prev_slot = __ldcg(a.pairs + 2 * pair), cur_slot = __ldcg(a.pairs + 2 * pair + 1);   // L2: the scan kernel rewrites the list
     const int tmr = MR ? a.tmr : 1;
     const int X0 = tx * a.tmb * G::MB, Y0 = ty * tmr * B;
     const int nj = min(a.tmb, a.nmbx - tx * a.tmb);                    // macro-blocks in a row of this tile
@@ -864,6 +868,7 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
     if (nd > 0) {
         build_shifted_copies<PITCH>(a, s_raw, s_win, tid, (int)blockDim.x);
         __syncthreads();
+        if (a.use_tma && tid == 0) mbar_inval(s_bar);                  // the scan kernel initialises it again for its next unit
     }
 
     // ---- candidate patches.  The magic numbers of the usual case come precomputed from the host: a
@@ -991,6 +996,15 @@ sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_const
         __threadfence();
         reduce_pair(a, pair, reinterpret_cast<unsigned *>(smem));
     }
+}
+
+template <int B, int NDY, int NQ, int PITCH, bool K64, int RB, int MAXT, int MINB, bool MR>
+__global__ void __launch_bounds__(MAXT, MINB)
+sad_search_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_constant__ CUtensorMap tm_ref,
+                  const SearchArgs a)
+{
+    extern __shared__ __align__(1024) uint8_t smem[];
+    search_tile<B, NDY, NQ, PITCH, K64, RB, MR>(tm_win, tm_ref, a, (int)blockIdx.x, smem);
 }
 
 } // namespace me

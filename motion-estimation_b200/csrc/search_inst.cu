@@ -3,6 +3,7 @@
 // multi-row tiles and the resident form are all instantiated here; me_api.cu picks by function pointer.
 #include "sad_search.cuh"
 #include "sad_persistent.cuh"
+#include "sad_scan.cuh"
 #include "kernel_choice.h"
 
 #if !defined(ME_INST_PITCH) || !defined(ME_INST_B)
@@ -21,6 +22,7 @@ KernelChoice choice()
     constexpr int CW = (B <= 16 && !K64) ? kConsumerWarps : kConsumerWarps32;
     k.fn_persistent = (const void *)&sad_search_persistent<B, kNDY, kNQ, PITCH, K64, RB, CW, kProducerWarps>;
     k.persist_threads = 32 * (kProducerWarps + CW);
+    if constexpr (!K64) k.fn_scan = (const void *)&sad_scan_kernel<B, kNDY, kNQ, PITCH, RB, kMaxThreads, 3>;
     k.ndy = kNDY; k.nq = kNQ; k.maxt = kMaxThreads; k.pitch = PITCH; k.rank_bits = RB;
     return k;
 }
