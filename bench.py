@@ -318,7 +318,7 @@ def run_search(args, rk, wl):
             n += 1
         t_cpu = time.perf_counter() - t_cpu
         cpu = {"value": n / t_cpu, "unit": "frame-pairs/s", "cores": osad.max_threads(), "kind": "port",
-               "sample": f"first {n} of the step's {P} pairs through oracle/sad_oracle.c (OpenMP, auto-vectorised scalar SAD), {t_cpu:.1f} s",
+               "sample": f"first {n} of the step's {P} pairs through oracle/sad_oracle.c (OpenMP over blocks, psadbw SAD), {t_cpu:.1f} s",
                "gcand_px_per_s": n * geo["cand_px_per_pair_valid"] / t_cpu / 1e9}
 
     line = {
@@ -490,7 +490,7 @@ def run_clip(args, rk):
     def pipeline(pre):
         f = frames
         if pre:
-            f = api.denoise_hf5(api.adaptive_histogram_equalization(f), n_list=len(f) + 1)
+            f = api.denoise_hf5(api.adaptive_histogram_equalization(f), n_list=len(f) + 1, distributed=False)   # every rank has its own recording
         return api.end_process(f, firstFrame=0, timestamps_ms=stamps, return_details=True)
 
     pipeline(True)
@@ -588,12 +588,12 @@ def run_nlm(args, rk):
     clocks = sampler.result()
     est.close()
     api.set_defaults(device=rk.local)
-    api.denoise_hf5(frames, n_list=len(frames) + 1)
+    api.denoise_hf5(frames, n_list=len(frames) + 1, distributed=False)          # every rank denoises its own frames (weak scaling)
     rk.barrier()
     t0 = time.perf_counter()
     reps = max(1, min(args.steps, 5))
     for _ in range(reps):
-        clean = api.denoise_hf5(frames, n_list=len(frames) + 1)          # host frames in, host frames out
+        clean = api.denoise_hf5(frames, n_list=len(frames) + 1, distributed=False)          # host frames in, host frames out
     rk.barrier()
     e2e_s = rk.max(time.perf_counter() - t0) / reps
     api.close_engines()

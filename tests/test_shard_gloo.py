@@ -52,3 +52,36 @@ def test_two_ranks_return_the_single_rank_series(n_pairs):
         got = np.frombuffer(ret[r], PAIR_DTYPE)
         assert got.tobytes() == want.tobytes(), f"rank {r}"
     assert [round(float(v)) for v in want["pdx"]] == [int(s[0]) for s in shifts]
+
+
+def test_round_bookkeeping_of_the_sharded_consecutive_search():
+    """Host logic of shard.search_consecutive_sharded without GPUs: every rank takes part in the same number of gather
+    rounds, a round carries min(chunk, what is left of the rank's slice) records per rank, and putting the rounds back
+    together gives the pair series in order -- for slices of unequal length and a last round that some ranks sit out."""
+    sys.path.insert(0, ROOT)
+    from motion_estimation_b200 import shard
+    from motion_estimation_b200.engine import PAIR_DTYPE
+
+    class FakeGather:                       # what RecordGather.wait returns: the ranks' records of one round, concatenated
+        def __init__(self, n_pairs, world, chunk):
+            self.n_pairs, self.world, self.chunk = n_pairs, world, chunk
+
+        def wait(self, ticket, counts):
+            parts = []
+            for r, c in enumerate(counts):
+                lo, _ = shard.shard_range(self.n_pairs, r, self.world)
+                rec = np.zeros(c, PAIR_DTYPE)
+                rec["nvalid_x"] = np.arange(lo + ticket * self.chunk, lo + ticket * self.chunk + c)     # the global pair index
+                parts.append(rec)
+            return np.concatenate(parts)
+
+    for n_pairs, world, chunk in ((23, 2, 4), (7, 4, 3), (5, 8, 2), (64, 8, 8), (1, 2, 4)):
+        per = -(-n_pairs // world)
+        chunk = max(1, min(chunk, per))
+        rounds = -(-per // chunk)
+        parts = [[] for _ in range(world)]
+        g = FakeGather(n_pairs, world, chunk)
+        for i in range(rounds):
+            shard._collect(g, i, i, chunk, n_pairs, world, parts)
+        got = np.concatenate([np.concatenate(p) if p else np.zeros(0, PAIR_DTYPE) for p in parts])
+        assert got["nvalid_x"].tolist() == list(range(n_pairs)), (n_pairs, world, chunk)
