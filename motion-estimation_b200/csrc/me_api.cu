@@ -1111,6 +1111,7 @@ int anchored_scan_device(me_ctx *c, int anchor_slot, int first_slot, int n_frame
     sc.pairs = c->d_pairs;
     sc.state = reinterpret_cast<int *>(c->d_scan + rec_bytes);
     sc.sync = reinterpret_cast<unsigned *>(c->d_scan + rec_bytes + 64);
+    sc.trace = env_int("ME_SCAN_TRACE", 0) ? reinterpret_cast<unsigned long long *>(c->d_scan + rec_bytes + 96) : nullptr;
     const long long most = (long long)a.tiles_per_pair * a.nsx * a.nsy * sc.max_look;      // units of the largest batch
     // every CTA of the grid arrives at every barrier, with or without work: no more CTAs per SM than ME_SCAN_CTAS (tuned: see DESIGN.md 4)
     const int cap = env_int("ME_SCAN_CTAS", 4);
@@ -1132,6 +1133,13 @@ int anchored_scan_device(me_ctx *c, int anchor_slot, int first_slot, int n_frame
     if (state[7]) {
         report_search_timeout(c);
         return fail(ME_ECUDA, "the resident scan kernel gave up waiting at a grid barrier; the context has been reset");
+    }
+    if (sc.trace) {
+        unsigned long long tr[2];
+        CU_TRY(cudaMemcpy(tr, sc.trace, sizeof tr, cudaMemcpyDeviceToHost));
+        fprintf(stderr, "[me_b200] scan trace: %d steps, CTA 0: %.2f us per step in search_tile, %.2f us per step at the barrier (grid %lld x %d threads, %d units per pair)\n",
+                state[6], tr[0] * 1e-3 / (state[6] ? state[6] : 1), tr[1] * 1e-3 / (state[6] ? state[6] : 1), grid, c->threads,
+                a.tiles_per_pair * a.nsx * a.nsy);
     }
     if (searches) *searches = state[5];
     if (launches) *launches = state[6];

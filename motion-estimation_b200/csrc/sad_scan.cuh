@@ -23,6 +23,7 @@ struct ScanArgs {
     int32_t *pairs;                            // the search's pair list (SearchArgs::pairs), rewritten per step
     unsigned *sync;                            // [0] arrivals, [1] generation; zero on entry
     int *state;                                // [0] batch size L (0 = done) [1] k [2] anchor [3] look [4] since [5] searches [6] steps [7] error
+    unsigned long long *trace;                 // debug (ME_SCAN_TRACE=1): [0] ns CTA 0 spent in search_tile, [1] ns it spent in barriers, else null
 };
 
 // All CTAs of the (cooperative, co-resident) grid; `last_arriver()` runs in one thread of the CTA that completes the barrier,
@@ -83,10 +84,13 @@ sad_scan_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_constan
     for (;;) {
         const int L = *reinterpret_cast<volatile int *>(sc.state);
         if (L == 0) break;
+        unsigned long long t0 = 0, t1 = 0, t2 = 0;
+        if (sc.trace && blockIdx.x == 0 && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
         for (int u = blockIdx.x; u < per_pair * L; u += gridDim.x) {
             search_tile<B, NDY, NQ, PITCH, false, RB, false>(tm_win, tm_ref, a, u, smem);
             __syncthreads();                                           // the next unit reuses the shared memory
         }
+        if (sc.trace && blockIdx.x == 0 && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
         const bool ok = scan_grid_sync(sc, [&] {
             const int k = sc.state[1], anchor = sc.state[2], look = sc.state[3], since = sc.state[4];
             int acc = -1;
@@ -114,6 +118,10 @@ sad_scan_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_constan
                 scan_write_batch(sc, anchor, k + L, min(2 * look, sc.max_look));
             }
         });
+        if (sc.trace && blockIdx.x == 0 && threadIdx.x == 0) {
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t2));
+            sc.trace[0] += t1 - t0; sc.trace[1] += t2 - t1;
+        }
         if (!ok) return;
     }
 }
