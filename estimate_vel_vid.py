@@ -39,6 +39,8 @@ def parse(argv=None):
                     help="search range in full-resolution pixels (default 64 = 32 of the reference's half-resolution pixels)")
     ap.add_argument("--range-y", type=int, default=0, dest="range_y",
                     help="vertical search range (default 0 = the same as --range); the recordings move along x, a small value is several times faster")
+    ap.add_argument("--min-range", type=int, default=6, dest="min_range",
+                    help="texture gate: a block takes part when max - min of its pixels reaches this many grey levels (default 6)")
     ap.add_argument("--units", choices=("reference", "fullres"), default="reference",
                     help="'reference' halves displacements like the reference's half-resolution ECC result")
     ap.add_argument("--device", type=int, default=0)
@@ -106,7 +108,7 @@ def main(argv=None):
     if len(frames) < 2:
         sys.exit("need at least two frames")
     number_list = list(range(first, first + len(frames) + 1))
-    cfg = me.SearchConfig(block=a.block, range=a.search_range, range_y=a.range_y)
+    cfg = me.SearchConfig(block=a.block, range=a.search_range, range_y=a.range_y, min_range=a.min_range)
     res = api.end_process(frames, imagePath=src, firstFrame=first, numberList=number_list, config=cfg,
                           device=a.device, units=a.units, return_details=True)
     out_dir = str(a.out) if a.out else (src if os.access(src, os.W_OK) else os.getcwd())

@@ -13,7 +13,7 @@ def test_calc_ecc_transform_signature_units_and_sign(me, golden_clips):
     from motion_estimation_b200 import api
     f = golden_clips["29.1"]["frames"]
     pdx, pdy, flag = api.calc_ECC_transform(f[0], f[4])
-    o = osad.search(f[0], f[4], 16, api.default_config.range)
+    o = osad.search(f[0], f[4], 16, api.default_config.range, min_range=api.default_config.min_range)
     assert flag == 1 and pdx == np.float32(o["pdx"] * np.float32(0.5)) and pdy == np.float32(o["pdy"] * np.float32(0.5))
     fx, fy, _ = api.calc_ECC_transform(f[0], f[4], units="fullres")
     assert (fx, fy) == (o["pdx"], o["pdy"])
@@ -53,7 +53,7 @@ def test_end_process_equals_serial_oracle_loop(me, golden_clips, name):
     stamps = [0.0] * first + [float(t) for t in g["stamps_ms"]]
 
     def pair(a, k):
-        o = osad.search(f[a], f[k], 16, api.default_config.range)
+        o = osad.search(f[a], f[k], 16, api.default_config.range, min_range=api.default_config.min_range)
         h = np.float32(0.5)
         return np.float32(o["pdx"] * h), np.float32(o["pdy"] * h), o["flag"]
 
@@ -105,7 +105,7 @@ def test_end_process_raw_flavour(me, golden_clips):
     stamps = [int(round(t * 1000)) for t in golden_clips["116.4"]["stamps_ms"][:12]]
     info, vx, vy, ts = api.end_process_raw(f, stamps, max_pairs=4)
     assert len(info) == 11
-    o = osad.search(f[3], f[4], 16, api.default_config.range)
+    o = osad.search(f[3], f[4], 16, api.default_config.range, min_range=api.default_config.min_range)
     t = stamps[4] / 10E+6
     # same operand types as the reference: float32 displacement, Python numbers for the rest (estimate_vel.py:362-366)
     assert info[3] == ((o["pdx"] / 611) / (t / 60), (o["pdy"] / 611) / (t / 60), t)
@@ -116,10 +116,11 @@ def test_dense_flow_mean(me, golden_clips):
     from motion_estimation_b200 import api
     f = golden_clips["29.1"]["frames"]
     mx, my = api.calculate_dense_flow(f[5], f[6])
-    o = osad.search(f[5], f[6], 16, api.default_config.range)
+    o = osad.search(f[5], f[6], 16, api.default_config.range, min_range=api.default_config.min_range)
     # the frame mean of the valid block vectors, reduced on the GPU with the median: equal to the oracle's (spec "mean"),
     # and next to the median (the reference's Farneback mean on this pair is -0.17 px for a 10.9 px jump -- it does not
     # track these recordings at all; tests/test_gpu_dense_flow.py compares the two where Farneback converges)
     assert (np.float32(mx), np.float32(my)) == (o["mean_dx"], o["mean_dy"])
-    assert abs(mx - float(o["pdx"])) < 2.0 and abs(my - float(o["pdy"])) < 1.0 and mx > 5     # a mean feels the outliers a median ignores
+    # a mean feels the outliers a median ignores (a few blocks of this dark frame lock onto other minima): 8.0 against a median of 10.9
+    assert abs(mx - float(o["pdx"])) < 3.5 and abs(my - float(o["pdy"])) < 1.0 and mx > 5
     api.close_engines()

@@ -55,10 +55,11 @@ def test_preprocessing_reproduces_the_frames_the_reference_ran_on(me, name):
 
 
 # share of the reference's converged pairs the GPU search must match within 0.3 half-resolution pixels, and the median
-# |difference| allowed: measured 0.965 / 0.838 / 0.755 and 0.063 / 0.109 / 0.134 px.  The misses are pairs across a
-# frame-drop gap (40+ px of motion): non-local means has smeared those frames over 9 neighbours, the per-block minima
-# scatter and the median falls short of the global ECC fit.
-PAIR_BARS = {"29.1": (0.95, 0.08), "58.2": (0.82, 0.13), "116.4": (0.74, 0.16)}
+# |difference| allowed: measured 0.993 / 0.929 / 0.805 and 0.061 / 0.083 / 0.114 px at the drop-in's default configuration
+# (0.965 / 0.838 / 0.755 with the library's texture gate of 2 grey levels).  The misses are pairs across a frame-drop gap
+# (40+ px of motion): non-local means has smeared those frames over 9 neighbours, the per-block minima scatter and the
+# median falls short of the global ECC fit.
+PAIR_BARS = {"29.1": (0.98, 0.08), "58.2": (0.91, 0.10), "116.4": (0.79, 0.13)}
 
 
 @pytest.mark.parametrize("name", NAMES)
@@ -66,7 +67,8 @@ def test_pair_displacements_vs_reference_ecc_on_cleaned_frames(me, name):
     _, clean = clip_frames(name)
     g = np.load(os.path.join(CLIPS, name, "reference_pairs.npz"))
     ks = g["k"]
-    cfg = me.SearchConfig()                                                  # the drop-in default
+    from motion_estimation_b200 import api
+    cfg = api.default_config                                                 # the drop-in default
     with me.MotionEstimator(clean.shape[1], clean.shape[2], cfg, max_frames=len(clean), max_pairs=len(ks)) as est:
         est.upload(clean)
         rec = est.search([(int(k), int(k) + 1) for k in ks])
@@ -97,13 +99,13 @@ def test_end_process_vs_reference_end_process(me, name):
     assert 0.85 * len(ref_v) <= len(ours_v) <= 1.15 * len(ref_v)                       # about the same pairs get accepted
     q_ours, q_ref = np.percentile(ours_v, [25, 50, 75]), np.percentile(ref_v, [25, 50, 75])
     print(f"{name}: velocity rows 25/50/75 % ours {np.round(q_ours, 2)} reference {np.round(q_ref, 2)}")
-    assert np.all(np.abs(q_ours - q_ref) <= 0.15 * q_ref), (name, q_ours, q_ref)       # measured: median within 9 %
+    assert np.all(np.abs(q_ours - q_ref) <= 0.16 * q_ref), (name, q_ours, q_ref)       # measured: within 14 / 4 / 3 %
     ok = (ref_v >= 0) & (ref_v < 200)
     ref_travel = float(np.diff(np.concatenate([[0.0], ref["motion"]]))[ok].sum())
     ours_travel = res.motion_list_opt[-1]
     print(f"{name}: travel ours {ours_travel:.3f} mm, reference over its plausible rows {ref_travel:.3f} mm")
-    # measured -7 % / -18 % / -27 %: the block median under-reads the smeared frames of the fast stretches (see above)
-    assert 0.70 * ref_travel <= ours_travel <= 1.05 * ref_travel, (name, ours_travel, ref_travel)
+    # measured -5 % / -13 % / -9 %: the block median under-reads the smeared frames of the fast stretches (see above)
+    assert 0.84 * ref_travel <= ours_travel <= 1.05 * ref_travel, (name, ours_travel, ref_travel)
     # no diverged rows: nothing negative, nothing beyond what a 64 px jump in one 5.5 ms frame interval can give (the
     # reference's rows on these stretches run from -295 to +286 mm/min)
     assert ours_v.min() >= 0 and ours_v.max() < (32 / 611) / (5.5e-3 / 60)
