@@ -1118,7 +1118,7 @@ int anchored_scan_device(me_ctx *c, int anchor_slot, int first_slot, int n_frame
     if (cap > 0 && per_sm > cap) per_sm = cap;
     long long grid = (long long)per_sm * c->sm_count;
     if (grid > most) grid = most;
-    CU_TRY(cudaMemsetAsync(c->d_scan + rec_bytes, 0, 128, st));
+    CU_TRY(cudaMemsetAsync(c->d_scan + rec_bytes, 0, 256, st));
     void *params[4] = {(void *)&c->tm_win, (void *)&c->tm_ref, (void *)&a, (void *)&sc};
     CU_TRY(cudaEventRecord(c->ev_k0, st));
     CU_TRY(cudaLaunchCooperativeKernel(c->kc.fn_scan, dim3((unsigned)grid), dim3((unsigned)c->threads), params, (size_t)c->smem, st));
@@ -1135,10 +1135,12 @@ int anchored_scan_device(me_ctx *c, int anchor_slot, int first_slot, int n_frame
         return fail(ME_ECUDA, "the resident scan kernel gave up waiting at a grid barrier; the context has been reset");
     }
     if (sc.trace) {
-        unsigned long long tr[2];
+        unsigned long long tr[6];
         CU_TRY(cudaMemcpy(tr, sc.trace, sizeof tr, cudaMemcpyDeviceToHost));
-        fprintf(stderr, "[me_b200] scan trace: %d steps, CTA 0: %.2f us per step in search_tile, %.2f us per step at the barrier (grid %lld x %d threads, %d units per pair)\n",
-                state[6], tr[0] * 1e-3 / (state[6] ? state[6] : 1), tr[1] * 1e-3 / (state[6] ? state[6] : 1), grid, c->threads,
+        const double n = state[6] ? state[6] : 1;
+        fprintf(stderr, "[me_b200] scan trace: %d steps (mean batch %.2f pairs), per step: CTA 0 %.2f us in search_tile + %.2f us at the barrier; "
+                "step start -> last CTA arrives %.2f us, the gate %.2f us (grid %lld x %d threads, %d units per pair)\n",
+                state[6], tr[5] / n, tr[0] * 1e-3 / n, tr[1] * 1e-3 / n, tr[2] * 1e-3 / n, tr[3] * 1e-3 / n, grid, c->threads,
                 a.tiles_per_pair * a.nsx * a.nsy);
     }
     if (searches) *searches = state[5];

@@ -85,13 +85,15 @@ sad_scan_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_constan
         const int L = *reinterpret_cast<volatile int *>(sc.state);
         if (L == 0) break;
         unsigned long long t0 = 0, t1 = 0, t2 = 0;
-        if (sc.trace && blockIdx.x == 0 && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        if (sc.trace && blockIdx.x == 0 && threadIdx.x == 0) { asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0)); sc.trace[4] = t0; }
         for (int u = blockIdx.x; u < per_pair * L; u += gridDim.x) {
             search_tile<B, NDY, NQ, PITCH, false, RB, false>(tm_win, tm_ref, a, u, smem);
             __syncthreads();                                           // the next unit reuses the shared memory
         }
         if (sc.trace && blockIdx.x == 0 && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
         const bool ok = scan_grid_sync(sc, [&] {
+            unsigned long long ta = 0, tb = 0;
+            if (sc.trace) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ta));
             const int k = sc.state[1], anchor = sc.state[2], look = sc.state[3], since = sc.state[4];
             int acc = -1;
             for (int i = 0; i < L; ++i) {
@@ -116,6 +118,12 @@ sad_scan_kernel(const __grid_constant__ CUtensorMap tm_win, const __grid_constan
             } else {
                 sc.state[4] = since + L;
                 scan_write_batch(sc, anchor, k + L, min(2 * look, sc.max_look));
+            }
+            if (sc.trace) {                                             // [2] step start (CTA 0) -> last arrival, [3] the gate, [5] sum of L
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tb));
+                sc.trace[2] += ta - *reinterpret_cast<volatile unsigned long long *>(sc.trace + 4);
+                sc.trace[3] += tb - ta;
+                sc.trace[5] += (unsigned long long)L;
             }
         });
         if (sc.trace && blockIdx.x == 0 && threadIdx.x == 0) {
