@@ -261,12 +261,12 @@ def run_search(args, rk, wl):
                 ticket = gather.start(est, P)
                 if prev is not None:
                     out = gather.wait(prev, counts)
-                prev = ticket
             else:
-                out = est.fetch_pairs(P)
-        if gather:
-            out = gather.wait(prev, counts)
-        return out
+                ticket = est.last_ticket()
+                if prev is not None:
+                    out = est.fetch_pairs(P, ticket=prev)                    # step k-1's records while step k searches: no idle gap
+            prev = ticket
+        return gather.wait(prev, counts) if gather else est.fetch_pairs(P, ticket=prev)
 
     e2e_steps(max(args.warmup, 2))
     rk.barrier()

@@ -156,6 +156,15 @@ int me_search(me_ctx *ctx, const int32_t *pairs, int n_pairs);
 /* Wait for the last me_search and copy its per-pair records to `out` (n_pairs of them). */
 int me_fetch_pairs(me_ctx *ctx, me_pair_result *out, int n_pairs);
 
+/* Searches in flight.  me_search only queues work: it may be called again before the records of the search before it were
+ * fetched (pair lists and pair records live in a ring of four slots; the per-block records do not -- me_fetch_blocks always
+ * sees the most recent search).  me_last_ticket names the search just launched; me_fetch_pairs_ticket waits for THAT search
+ * only (on a stream of its own, not behind the searches launched after it) and copies its records.  A ticket is valid until
+ * three more searches have been launched.  Keeping two searches in flight removes the idle gap between a search and the
+ * launch of the next one: batch users of the reference's consecutive-pair loop (estimate_vel.py:333-378). */
+int me_last_ticket(const me_ctx *ctx);
+int me_fetch_pairs_ticket(me_ctx *ctx, int ticket, me_pair_result *out, int n_pairs);
+
 /* Per-block results of pair `pair_index` of the last me_search; any pointer may be NULL.
  * Layouts (row-major over by, bx): mv int16[nb][2] (dx,dy); sad uint32[nb]; sub float[nb][2];
  * flags uint8[nb].  This is the dense field the reference only has through Farneback

@@ -133,6 +133,9 @@ def lib():
     L.me_download.argtypes = [vp, vp, C.c_size_t, C.c_int, C.c_int]
     L.me_search.argtypes = [vp, i32p, C.c_int]
     L.me_fetch_pairs.argtypes = [vp, C.POINTER(PairResult), C.c_int]
+    L.me_fetch_pairs_ticket.argtypes = [vp, C.c_int, C.POINTER(PairResult), C.c_int]
+    L.me_last_ticket.argtypes = [vp]
+    L.me_last_ticket.restype = C.c_int
     L.me_fetch_blocks.argtypes = [vp, C.c_int, vp, vp, vp, vp]
     L.me_estimate_pair.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(PairResult)]
     L.me_search_device.argtypes = [vp, vp, C.c_size_t, C.c_int, i32p, C.c_int, vp]
@@ -155,7 +158,8 @@ def lib():
     for name in ("me_clahe", "me_denoise", "me_download", "me_create", "me_destroy", "me_get_geometry", "me_upload", "me_upload_bgr", "me_search",
                  "me_fetch_pairs", "me_fetch_blocks", "me_estimate_pair", "me_search_device", "me_sync",
                  "me_last_search_ms", "me_microbench_vabsdiff4", "me_timer_start", "me_timer_stop", "me_copy_timer_start",
-                 "me_copy_timer_stop", "me_anchored_scan", "me_copy_pair_records_device", "me_copy_frames_device"):
+                 "me_copy_timer_stop", "me_anchored_scan", "me_copy_pair_records_device", "me_copy_frames_device",
+                 "me_fetch_pairs_ticket"):
         getattr(L, name).restype = C.c_int
     _lib = L
     return L

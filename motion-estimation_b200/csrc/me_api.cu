@@ -174,8 +174,17 @@ struct me_ctx {
     SearchRecord recent[4];
     int recent_next = 0;
     // pairs + results
+    // Pair lists and pair records live in a ring of kSearchRing slots (slot s at base + s * max_pairs entries), so that a search
+    // can be queued while the one before it still runs and its records have not been fetched: me_search never waits for the
+    // previous search, only for the one kSearchRing launches ago.
+    static constexpr int kSearchRing = 4;
     int32_t *h_pairs = nullptr, *d_pairs = nullptr;
     me_pair_result *h_pair_out = nullptr;
+    int slot = 0;                                  // ring slot (= ticket) of the most recent search
+    cudaEvent_t ev_slot[kSearchRing] = {nullptr, nullptr, nullptr, nullptr};
+    bool slot_used[kSearchRing] = {false, false, false, false};
+    int slot_pairs[kSearchRing] = {0, 0, 0, 0};
+    cudaStream_t s_fetch = nullptr;                // record fetches: neither behind queued searches nor behind frame uploads
     int last_pairs = 0;
     // launch configuration
     me::SearchArgs args{};
@@ -433,11 +442,12 @@ const me_ctx *pick_plan(const me_ctx *c, int n_pairs)
 
 // pl: the plan (c itself or c->big); frame_pitch 0 = the context's ring layout.
 int launch_search(me_ctx *c, const me_ctx *pl, const uint8_t *frames, const CUtensorMap &tm_win, const CUtensorMap &tm_ref,
-                  int n_pairs, cudaStream_t st, size_t frame_pitch = 0)
+                  int n_pairs, cudaStream_t st, size_t frame_pitch = 0, int slot = 0)
 {
     me::SearchArgs a = pl->args;
     a.frames = frames;
-    a.pairs = c->d_pairs;
+    a.pairs = c->d_pairs + (size_t)slot * 2 * c->max_pairs;
+    a.pair_out = a.pair_out + (size_t)slot * c->max_pairs;
     if (frame_pitch) { a.frame_pitch = (int)frame_pitch; a.frame_stride = (long long)frame_pitch * c->H; }
     const long long units = (long long)a.tiles_per_pair * n_pairs * a.nsx * a.nsy;
     if (c->have_rec) { CU_TRY(cudaStreamWaitEvent(st, c->ev_rec, 0)); c->have_rec = false; }
@@ -677,15 +687,17 @@ int me_create(int device, int height, int width, const me_params *params, int ma
         CREATE_TRY(cudaHostAlloc(&c->h_stage[i], c->stage_bytes, cudaHostAllocDefault));
         CREATE_TRY(cudaEventCreateWithFlags(&c->stage_free[i], cudaEventDisableTiming));
     }
-    CREATE_TRY(cudaHostAlloc(&c->h_pairs, sizeof(int32_t) * 2 * (size_t)max_pairs, cudaHostAllocDefault));
+    CREATE_TRY(cudaStreamCreateWithFlags(&c->s_fetch, cudaStreamNonBlocking));
+    for (auto &e : c->ev_slot) CREATE_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CREATE_TRY(cudaHostAlloc(&c->h_pairs, sizeof(int32_t) * 2 * (size_t)max_pairs * me_ctx::kSearchRing, cudaHostAllocDefault));
     CREATE_TRY(cudaHostAlloc(&c->h_pair_out, sizeof(me_pair_result) * ((size_t)max_pairs + 1), cudaHostAllocDefault));   // + the error word of the scan
-    CREATE_TRY(cudaMalloc(&c->d_pairs, sizeof(int32_t) * 2 * (size_t)max_pairs));
+    CREATE_TRY(cudaMalloc(&c->d_pairs, sizeof(int32_t) * 2 * (size_t)max_pairs * me_ctx::kSearchRing));
     const size_t nb = (size_t)c->args.nb * (size_t)max_pairs;
     CREATE_TRY(cudaMalloc(&c->args.blk_mv, nb * 2 * sizeof(int16_t)));
     CREATE_TRY(cudaMalloc(&c->args.blk_sad, nb * sizeof(uint32_t)));
     CREATE_TRY(cudaMalloc(&c->args.blk_sub, nb * 2 * sizeof(float)));
     CREATE_TRY(cudaMalloc(&c->args.blk_flags, nb));
-    CREATE_TRY(cudaMalloc(&c->args.pair_out, sizeof(me_pair_result) * (size_t)max_pairs));
+    CREATE_TRY(cudaMalloc(&c->args.pair_out, sizeof(me_pair_result) * (size_t)max_pairs * me_ctx::kSearchRing));
     CREATE_TRY(cudaMalloc(&c->args.pair_ticket, sizeof(unsigned) * (size_t)max_pairs));
     CREATE_TRY(cudaMemset(c->args.pair_ticket, 0, sizeof(unsigned) * (size_t)max_pairs));
     const bool big_slabs = c->big && c->big->args.nsx * c->big->args.nsy > 1;
@@ -742,6 +754,8 @@ int me_destroy(me_ctx *c)
     if (c->h_pair_out) cudaFreeHost(c->h_pair_out);
     if (c->ev_upload) cudaEventDestroy(c->ev_upload);
     if (c->ev_search) cudaEventDestroy(c->ev_search);
+    for (auto &e : c->ev_slot) if (e) cudaEventDestroy(e);
+    if (c->s_fetch) { cudaStreamSynchronize(c->s_fetch); cudaStreamDestroy(c->s_fetch); }
     if (c->ev_k0) cudaEventDestroy(c->ev_k0);
     if (c->ev_k1) cudaEventDestroy(c->ev_k1);
     if (c->ev_t0) cudaEventDestroy(c->ev_t0);
@@ -984,13 +998,17 @@ int me_search(me_ctx *c, const int32_t *pairs, int n_pairs)
     int rc = check_pairs(c, pairs, n_pairs, c->max_frames);
     if (rc) return rc;
     CU_TRY(cudaSetDevice(c->device));
-    if (c->have_search) CU_TRY(cudaEventSynchronize(c->ev_search));   // h_pairs is about to be rewritten
-    memcpy(c->h_pairs, pairs, sizeof(int32_t) * 2 * (size_t)n_pairs);
-    CU_TRY(cudaMemcpyAsync(c->d_pairs, c->h_pairs, sizeof(int32_t) * 2 * (size_t)n_pairs, cudaMemcpyHostToDevice, c->s_compute));
+    const int slot = (c->slot + 1) % me_ctx::kSearchRing;
+    if (c->slot_used[slot]) CU_TRY(cudaEventSynchronize(c->ev_slot[slot]));   // the search four launches ago: its pair list is about to be rewritten
+    int32_t *hp = c->h_pairs + (size_t)slot * 2 * c->max_pairs, *dp = c->d_pairs + (size_t)slot * 2 * c->max_pairs;
+    memcpy(hp, pairs, sizeof(int32_t) * 2 * (size_t)n_pairs);
+    CU_TRY(cudaMemcpyAsync(dp, hp, sizeof(int32_t) * 2 * (size_t)n_pairs, cudaMemcpyHostToDevice, c->s_compute));
     if (c->have_upload) CU_TRY(cudaStreamWaitEvent(c->s_compute, c->ev_upload, 0));
     const me_ctx *pl = pick_plan(c, n_pairs);
-    rc = launch_search(c, pl, c->d_frames, pl->tm_win, pl->tm_ref, n_pairs, c->s_compute);
+    rc = launch_search(c, pl, c->d_frames, pl->tm_win, pl->tm_ref, n_pairs, c->s_compute, 0, slot);
     if (rc) return rc;
+    CU_TRY(cudaEventRecord(c->ev_slot[slot], c->s_compute));
+    c->slot = slot; c->slot_used[slot] = true; c->slot_pairs[slot] = n_pairs;
     CU_TRY(cudaEventRecord(c->ev_search, c->s_compute));
     {
         me_ctx::SearchRecord &r = c->recent[c->recent_next];
@@ -1020,11 +1038,15 @@ int me_search_device(me_ctx *c, const uint8_t *d_frames, size_t pitch, int n_fra
     rc = make_tensor_map(&tw, d_frames, c->W, c->H, n_frames, pitch, pl->win_pitch, pl->args.box_rows);
     if (!rc) rc = make_tensor_map(&tr, d_frames, c->W, c->H, n_frames, pitch, me::kRefPitch, c->p.block * pl->args.tmr);
     if (rc) return rc;
-    if (c->have_search) CU_TRY(cudaEventSynchronize(c->ev_search));
-    memcpy(c->h_pairs, pairs, sizeof(int32_t) * 2 * (size_t)n_pairs);
-    CU_TRY(cudaMemcpyAsync(c->d_pairs, c->h_pairs, sizeof(int32_t) * 2 * (size_t)n_pairs, cudaMemcpyHostToDevice, st));
-    rc = launch_search(c, pl, d_frames, tw, tr, n_pairs, st, pitch);
+    const int slot = (c->slot + 1) % me_ctx::kSearchRing;
+    if (c->slot_used[slot]) CU_TRY(cudaEventSynchronize(c->ev_slot[slot]));
+    int32_t *hp = c->h_pairs + (size_t)slot * 2 * c->max_pairs, *dp = c->d_pairs + (size_t)slot * 2 * c->max_pairs;
+    memcpy(hp, pairs, sizeof(int32_t) * 2 * (size_t)n_pairs);
+    CU_TRY(cudaMemcpyAsync(dp, hp, sizeof(int32_t) * 2 * (size_t)n_pairs, cudaMemcpyHostToDevice, st));
+    rc = launch_search(c, pl, d_frames, tw, tr, n_pairs, st, pitch, slot);
     if (rc) return rc;
+    CU_TRY(cudaEventRecord(c->ev_slot[slot], st));
+    c->slot = slot; c->slot_used[slot] = true; c->slot_pairs[slot] = n_pairs;
     CU_TRY(cudaEventRecord(c->ev_search, st));
     if (st != c->s_compute) CU_TRY(cudaStreamWaitEvent(c->s_compute, c->ev_search, 0));
     c->have_search = true;
@@ -1032,20 +1054,32 @@ int me_search_device(me_ctx *c, const uint8_t *d_frames, size_t pitch, int n_fra
     return ME_OK;
 }
 
-int me_fetch_pairs(me_ctx *c, me_pair_result *out, int n_pairs)
+int me_last_ticket(const me_ctx *c) { return c ? c->slot : 0; }
+
+int me_fetch_pairs_ticket(me_ctx *c, int ticket, me_pair_result *out, int n_pairs)
 {
     if (!c || !out) return fail(ME_EINVAL, "NULL argument");
     if (!c->have_search) return fail(ME_ESTATE, "me_fetch_pairs before any me_search");
-    if (n_pairs < 1 || n_pairs > c->last_pairs) return fail(ME_EINVAL, "n_pairs=%d, last search had %d", n_pairs, c->last_pairs);
+    if (ticket < 0 || ticket >= me_ctx::kSearchRing || !c->slot_used[ticket])
+        return fail(ME_EINVAL, "ticket %d does not name one of the last %d searches", ticket, me_ctx::kSearchRing);
+    if (n_pairs < 1 || n_pairs > c->slot_pairs[ticket]) return fail(ME_EINVAL, "n_pairs=%d, that search had %d", n_pairs, c->slot_pairs[ticket]);
     CU_TRY(cudaSetDevice(c->device));
-    CU_TRY(cudaMemcpyAsync(c->h_pair_out, c->args.pair_out, sizeof(me_pair_result) * (size_t)n_pairs,
-                           cudaMemcpyDeviceToHost, c->s_compute));
-    int err = 0;
-    CU_TRY(cudaMemcpyAsync(&err, c->d_error, sizeof(int), cudaMemcpyDeviceToHost, c->s_compute));
-    CU_TRY(cudaStreamSynchronize(c->s_compute));
-    if (err) return report_search_timeout(c);
+    // on a stream of its own: a fetch queued on the compute stream would wait for the searches launched after the one it wants
+    int *h_err = reinterpret_cast<int *>(c->h_pair_out + c->max_pairs);
+    CU_TRY(cudaStreamWaitEvent(c->s_fetch, c->ev_slot[ticket], 0));
+    CU_TRY(cudaMemcpyAsync(c->h_pair_out, c->args.pair_out + (size_t)ticket * c->max_pairs, sizeof(me_pair_result) * (size_t)n_pairs,
+                           cudaMemcpyDeviceToHost, c->s_fetch));
+    CU_TRY(cudaMemcpyAsync(h_err, c->d_error, sizeof(int), cudaMemcpyDeviceToHost, c->s_fetch));
+    CU_TRY(cudaStreamSynchronize(c->s_fetch));
+    if (*h_err) return report_search_timeout(c);
     memcpy(out, c->h_pair_out, sizeof(me_pair_result) * (size_t)n_pairs);
     return ME_OK;
+}
+
+int me_fetch_pairs(me_ctx *c, me_pair_result *out, int n_pairs)
+{
+    if (!c) return fail(ME_EINVAL, "NULL argument");
+    return me_fetch_pairs_ticket(c, c->slot, out, n_pairs);
 }
 
 int me_fetch_blocks(me_ctx *c, int pair_index, int16_t *mv, uint32_t *sad, float *sub, uint8_t *flags)
@@ -1169,6 +1203,8 @@ int me_anchored_scan(me_ctx *c, int anchor_slot, int first_slot, int n_frames, f
         int rc = anchored_scan_device(c, anchor_slot, first_slot, n_frames, scale, gate, out, searches, launches, &done);
         if (rc) return rc;
         if (done) {
+            c->slot = 0; c->slot_used[0] = true; c->slot_pairs[0] = c->last_pairs;      // the walk uses ring slot 0
+            CU_TRY(cudaEventRecord(c->ev_slot[0], st));
             CU_TRY(cudaEventRecord(c->ev_search, st));
             me_ctx::SearchRecord &r = c->recent[c->recent_next];
             c->recent_next = (c->recent_next + 1) % 4;
@@ -1215,6 +1251,8 @@ int me_anchored_scan(me_ctx *c, int anchor_slot, int first_slot, int n_frames, f
             look = std::min(2 * look, max_look);                               // same anchor: look further
         }
     }
+    c->slot = 0; c->slot_used[0] = true; c->slot_pairs[0] = c->last_pairs;              // the walk uses ring slot 0
+    CU_TRY(cudaEventRecord(c->ev_slot[0], st));
     CU_TRY(cudaEventRecord(c->ev_search, st));
     {
         me_ctx::SearchRecord &r = c->recent[c->recent_next];
@@ -1294,7 +1332,8 @@ int me_copy_pair_records_device(me_ctx *c, void *d_dst, int n_pairs, void *strea
     CU_TRY(cudaSetDevice(c->device));
     cudaStream_t st = stream ? (cudaStream_t)stream : c->s_compute;
     if (st != c->s_compute) CU_TRY(cudaStreamWaitEvent(st, c->ev_search, 0));
-    CU_TRY(cudaMemcpyAsync(d_dst, c->args.pair_out, sizeof(me_pair_result) * (size_t)n_pairs, cudaMemcpyDeviceToDevice, st));
+    CU_TRY(cudaMemcpyAsync(d_dst, c->args.pair_out + (size_t)c->slot * c->max_pairs, sizeof(me_pair_result) * (size_t)n_pairs,
+                           cudaMemcpyDeviceToDevice, st));
     if (st != c->s_compute) {                        // later searches on the compute stream wait for this copy (launch_search)
         CU_TRY(cudaEventRecord(c->ev_rec, st));
         c->have_rec = true;

@@ -131,9 +131,17 @@ class MotionEstimator:
         check(self._L.me_search(self._ctx, ptr, p.shape[0]))
         return p.shape[0]
 
-    def fetch_pairs(self, n):
+    def last_ticket(self) -> int:
+        """Names the search just launched; valid until three more searches have been launched."""
+        return int(self._L.me_last_ticket(self._ctx))
+
+    def fetch_pairs(self, n, ticket=None):
+        """Records of the last search, or of the search `ticket` names (several searches may be in flight)."""
         out = np.zeros(n, PAIR_DTYPE)
-        check(self._L.me_fetch_pairs(self._ctx, out.ctypes.data_as(C.POINTER(PairResult)), int(n)))
+        if ticket is None:
+            check(self._L.me_fetch_pairs(self._ctx, out.ctypes.data_as(C.POINTER(PairResult)), int(n)))
+        else:
+            check(self._L.me_fetch_pairs_ticket(self._ctx, int(ticket), out.ctypes.data_as(C.POINTER(PairResult)), int(n)))
         return out
 
     def search(self, pairs):

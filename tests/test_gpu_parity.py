@@ -313,6 +313,31 @@ def test_rectangular_range_equals_oracle(me, monkeypatch, H, W, B, R, Ry, mode):
         assert one[0].tobytes() == res[3].tobytes()
 
 
+def test_searches_in_flight_and_ticketed_fetch(me):
+    """Several searches queued before any records are fetched: every ticket returns the records of its own search, whatever is
+    launched after it (four ring slots), and the plain fetch still means the last search."""
+    from motion_estimation_b200 import synth
+    H, W, n = 144, 320, 7
+    frames, _ = synth.translating_frames(n, H, W, 12, seed_texture=51, seed_motion=52)
+    cfg = me.SearchConfig(block=16, range=16)
+    batches = [[(0, 1), (1, 2)], [(2, 3)], [(3, 4), (4, 5), (5, 6)], [(6, 0), (5, 1)], [(1, 0)], [(2, 5), (3, 3)]]
+    with me.MotionEstimator(H, W, cfg, max_frames=n, max_pairs=3) as est:
+        est.upload(frames)
+        want = [est.search(b).copy() for b in batches]                      # one at a time
+        tickets = []
+        for i, b in enumerate(batches):
+            est.launch(b)
+            tickets.append(est.last_ticket())
+            if i >= 2:                                                       # keep three in flight, fetch the oldest
+                j = i - 2
+                assert est.fetch_pairs(len(batches[j]), ticket=tickets[j]).tobytes() == want[j].tobytes(), j
+        for j in (len(batches) - 2, len(batches) - 1):
+            assert est.fetch_pairs(len(batches[j]), ticket=tickets[j]).tobytes() == want[j].tobytes(), j
+        assert est.fetch_pairs(len(batches[-1])).tobytes() == want[-1].tobytes()
+        with pytest.raises(me.MEError):
+            est.fetch_pairs(3, ticket=tickets[-1])                           # that search had two pairs
+
+
 def test_resident_search_overlapping_denoise_on_the_copy_stream(me):
     """Pre-processing kernels run on the copy stream while a resident (one CTA per SM) search runs on the compute stream:
     NLM CTAs hold SMs, so not all resident CTAs need to be co-resident from the start.  Results and the kernel's error flag
