@@ -151,20 +151,21 @@ __global__ void __launch_bounds__(kNlmThreads, 2) nlm_kernel(const NlmArgs a)
                 for (int k = 0; k <= NW; ++k) w[k] = row[k];
 #pragma unroll
                 for (int k = 0; k < NW; ++k) d[k] = __vabsdiffu4(i0[rd][k], __funnelshift_r(w[k], w[k + 1], sft));
-                int px[NPX];
+                // squares first (independent of one another), then the sliding sum as one three-input add per output: a short
+                // dependent chain instead of 49 chained multiply-adds (the kernel is latency-bound at 4 warps per scheduler)
+                int sq[NPX];
 #pragma unroll
-                for (int x = 0; x < NPX; ++x) px[x] = (int)__byte_perm(d[x >> 2], 0u, 0x4440u | (unsigned)(x & 3));   // one PRMT per pixel
-                int sum = 0;
-#pragma unroll
-                for (int x = 0; x < TWS; ++x) sum += px[x] * px[x];
-                int out[S];
-                out[0] = sum;
-#pragma unroll
-                for (int c = 1; c < S; ++c) {
-                    sum += px[c + TWS - 1] * px[c + TWS - 1];
-                    sum -= px[c - 1] * px[c - 1];
-                    out[c] = sum;
+                for (int x = 0; x < NPX; ++x) {
+                    const int px = (int)__byte_perm(d[x >> 2], 0u, 0x4440u | (unsigned)(x & 3));                      // one PRMT per pixel
+                    sq[x] = px * px;
                 }
+                int part[4] = {0, 0, 0, 0};
+#pragma unroll
+                for (int x = 0; x < TWS; ++x) part[x & 3] += sq[x];
+                int out[S];
+                out[0] = (part[0] + part[1]) + (part[2] + part[3]);
+#pragma unroll
+                for (int c = 1; c < S; ++c) out[c] = out[c - 1] + sq[c + TWS - 1] - sq[c - 1];
                 int4 *dstp = reinterpret_cast<int4 *>(s_h + r * HP + seg * S);
 #pragma unroll
                 for (int e = 0; e < S / 4; ++e) dstp[e] = make_int4(out[4 * e], out[4 * e + 1], out[4 * e + 2], out[4 * e + 3]);
