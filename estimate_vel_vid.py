@@ -76,10 +76,28 @@ def save_cache(frames, cache_h5, cache_npy):
         np.save(cache_npy, frames)
 
 
+def ranks():
+    """(rank, world) when started under torchrun (one process per GPU): the non-local-means stage -- nine tenths of the run time --
+    then shards its frame ranges over the GPUs (api.denoise_hf5); everything else runs on rank 0.  (0, 1) otherwise."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world <= 1:
+        return 0, 1
+    import torch
+    import torch.distributed as dist
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return dist.get_rank(), dist.get_world_size()
+
+
 def main(argv=None):
     a, whole = parse(argv)
     import motion_estimation_b200 as me
     from motion_estimation_b200 import api, ingest
+    rank, world = ranks()
+    if world > 1:
+        a.device = int(os.environ.get("LOCAL_RANK", "0"))
 
     src = str(a.srcDirectory)
     first, last = (0, None) if whole else a.fileIndex
@@ -103,8 +121,12 @@ def main(argv=None):
             frames = api.adaptive_histogram_equalization(frames)
         if do_denoise:                                # reference :246-299: non-local means, bit-exact with cv2's
             frames = api.denoise_hf5(frames, n_list=len(frames) + 1)      # len(numberList) = frames + 1 (its line 73)
-        if (do_clahe or do_denoise) and os.access(src, os.W_OK):
+        if (do_clahe or do_denoise) and os.access(src, os.W_OK) and rank == 0:
             save_cache(frames, cache_h5, cache_npy)
+    if rank != 0:                                     # the pair loop is sequential inside a recording: rank 0 carries on alone
+        import torch.distributed as dist
+        dist.barrier()
+        return None
     if len(frames) < 2:
         sys.exit("need at least two frames")
     number_list = list(range(first, first + len(frames) + 1))
@@ -139,6 +161,9 @@ def main(argv=None):
               f"(+-{a.search_range} px): rerun with a larger --range")
     print(f"accepted pairs: {len(res.accepted_pairs)}; searches run: {res.searches} in {res.launches} launches")
     print(f"wrote {os.path.join(out_dir, 'velocity_estimates.csv')}")
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
     return res
 
 

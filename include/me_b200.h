@@ -220,7 +220,8 @@ int me_anchored_scan(me_ctx *ctx, int anchor_slot, int first_slot, int n_frames,
 /* Hand the per-pair records of the last search to another GPU consumer without a host bounce: copies n_pairs
  * records from the context's result buffer to d_dst (device memory of the same GPU, e.g. the send buffer of an
  * NCCL all_gather -- the one exchange step of the sharded path) on `stream`, ordered after the search.
- * Asynchronous. */
+ * Asynchronous.  `stream` NULL means the context's compute stream, NOT the CUDA default stream (whose handle is also 0): a
+ * consumer that runs on the default stream must pass a stream of its own here and order itself after it. */
 int me_copy_pair_records_device(me_ctx *ctx, void *d_dst, int n_pairs, void *stream);
 
 /* Integer-SAD issue-rate microbenchmark: runs a register-only VABSDIFF4 loop on every SM and

@@ -193,13 +193,17 @@ def gather_frames_sharded(local: "np.ndarray | None", est, first_slot, n_local, 
     world = dist.get_world_size(group)
     H, W = shape
     per = -(-n_total // world)
-    send = torch.zeros((per, H, W), dtype=torch.uint8, device="cuda")
-    if n_local:
-        st = torch.cuda.current_stream().cuda_stream
-        est.copy_frames_device(send.data_ptr(), W, first_slot, n_local, stream=st)
-    recv = torch.empty((world, per, H, W), dtype=torch.uint8, device="cuda")
-    dist.all_gather_into_tensor(recv, send, group=group)
-    host = recv.cpu().numpy()
+    # a stream of our own: torch's default stream has handle 0, which the C ABI reads as "the context's copy stream" --
+    # the copy and the collective must be on ONE stream, or the gather can read the send buffer before the copy landed
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):
+        send = torch.zeros((per, H, W), dtype=torch.uint8, device="cuda")
+        if n_local:
+            est.copy_frames_device(send.data_ptr(), W, first_slot, n_local, stream=side.cuda_stream)
+        recv = torch.empty((world, per, H, W), dtype=torch.uint8, device="cuda")
+        dist.all_gather_into_tensor(recv, send, group=group)
+        host = recv.cpu().numpy()
+    side.synchronize()
     out = np.empty((n_total, H, W), np.uint8)
     for r in range(world):
         lo, hi = shard_range(n_total, r, world)
