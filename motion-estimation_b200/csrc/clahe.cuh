@@ -55,19 +55,23 @@ __global__ void __launch_bounds__(256) clahe_lut_kernel(const ClaheArgs a, int f
         // are spread over the whole CTA and four loads are in flight per thread before the first histogram update (r02a ncu
         // of the one-row-per-warp form: 8.5 long-scoreboard stalls per issued instruction, 1.5 TB/s).
         const int w0 = xb >> 2, w1 = (xe + 3) >> 2, nw = w1 - w0, total = a.th * nw;
-        const unsigned magic = nw > 1 ? (unsigned)(0x100000000ull / (unsigned)nw + 1ull) : 0u;
+        // (row, word) of this thread's first pair, then steps of 256 pairs: incremental, no division per load
+        const int step_r = 256 / nw, step_c = 256 - step_r * nw;
+        int r = tid / nw, cw = tid - r * nw;
+        const bool inside = (tj + 1) * a.th <= a.H;                      // no reflected rows in this tile (all but a ragged last row of tiles)
         for (int p0 = tid; p0 < total; p0 += 4 * 256) {
             uint32_t v[4];
             int wi[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-                const int p = p0 + u * 256;
                 wi[u] = -1;
-                if (p < total) {
-                    const int r = magic ? (int)__umulhi((unsigned)p, magic) : p;
-                    wi[u] = w0 + p - r * nw;
-                    v[u] = __ldg(reinterpret_cast<const uint32_t *>(f + (size_t)reflect101(tj * a.th + r, a.H) * a.pitch) + wi[u]);
+                if (p0 + u * 256 < total) {
+                    wi[u] = w0 + cw;
+                    const int y = inside ? tj * a.th + r : reflect101(tj * a.th + r, a.H);
+                    v[u] = __ldg(reinterpret_cast<const uint32_t *>(f + (size_t)y * a.pitch) + wi[u]);
                 }
+                cw += step_c; r += step_r;
+                if (cw >= nw) { cw -= nw; ++r; }
             }
             if (((xb | xe) & 3) == 0) {                      // tile edges on word boundaries (the usual case): no per-byte tests
 #pragma unroll
@@ -217,9 +221,10 @@ __global__ void __launch_bounds__(256) clahe_apply_kernel(const ClaheArgs a, int
                 if (r >= rows) break;
                 const float ya = s_ya[r], ya1 = s_ya1[r];
                 const uint2 *trow = tab + (size_t)(s_cy[r] - cy_lo) * cells_x * 256;
-                uint32_t out = 0;
+                uint32_t q[4];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) out |= blend(trow[cell[i] + ((in[r] >> (8 * i)) & 255u)], xa[i], xa1[i], ya, ya1) << (8 * i);
+                for (int i = 0; i < 4; ++i) q[i] = blend(trow[cell[i] + ((in[r] >> (8 * i)) & 255u)], xa[i], xa1[i], ya, ya1);
+                const uint32_t out = __byte_perm(__byte_perm(q[0], q[1], 0x0040), __byte_perm(q[2], q[3], 0x0040), 0x5410);
                 *reinterpret_cast<uint32_t *>(reinterpret_cast<uint8_t *>(p0) + (size_t)r * a.pitch) = out;
             }
         }
