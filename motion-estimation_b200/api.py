@@ -92,10 +92,10 @@ def calc_ECC_transform(prevFrame, curFrame, *, config: Optional[SearchConfig] = 
     cur = np.ascontiguousarray(curFrame, dtype=np.uint8)
     if prev.ndim != 2 or prev.shape != cur.shape:
         raise ValueError("calc_ECC_transform expects two (H, W) uint8 frames of equal shape")
+    s = np.float32(_scale(units))                 # bad arguments are refused before any device work
     cfg = config or default_config
     eng = _engine(prev.shape[0], prev.shape[1], cfg, default_device if device is None else device, 2, 1)
     r = eng.estimate_pair(prev, cur)
-    s = np.float32(_scale(units))
     return np.float32(r["pdx"] * s), np.float32(r["pdy"] * s), int(r["flag"])
 
 
