@@ -124,3 +124,32 @@ def test_dense_flow_mean(me, golden_clips):
     # a mean feels the outliers a median ignores (a few blocks of this dark frame lock onto other minima): 8.0 against a median of 10.9
     assert abs(mx - float(o["pdx"])) < 3.5 and abs(my - float(o["pdy"])) < 1.0 and mx > 5
     api.close_engines()
+
+
+def test_end_process_static_stretch_longer_than_the_device_window(me):
+    """A static scene keeps the anchor for longer than the device ring holds frames: the anchor then lives in the spare slot
+    while the window slides on.  Also the smallest inputs: one frame (nothing to do) and two frames."""
+    from motion_estimation_b200 import api, synth, velocity
+    H, W = 64, 256
+    canvas = synth.texture(H + 8, W + 200, seed=9)
+    offs = [0, 5, 11, 16] + [16] * 30 + [22, 27, 33, 40, 40, 40, 46]           # moves, stands still for 30 frames, moves again
+    noise = np.random.default_rng(3).integers(-1, 2, size=(len(offs), H, W))
+    frames = np.clip(np.stack([canvas[4:4 + H, 150 - o:150 - o + W] for o in offs]).astype(np.int16) + noise, 0, 255).astype(np.uint8)
+    stamps = [5.531 * k for k in range(len(frames) + 3)]
+    cfg = me.SearchConfig(16, 16)
+
+    def pair(a, k):
+        o = osad.search(frames[a], frames[k], 16, 16)
+        return np.float32(o["pdx"] * np.float32(0.5)), np.float32(o["pdy"] * np.float32(0.5)), o["flag"]
+
+    lines = ["# timecode format v2"] + [repr(t) for t in stamps]
+    want = velocity.anchored_pair_loop(len(frames), pair, velocity.timecode_lookup(lines))
+    for ring, mp_ in ((6, 3), (9, 4), (64, 16)):
+        got = api.end_process(frames, timestamps_ms=stamps, config=cfg, ring_frames=ring, max_pairs=mp_, return_details=True)
+        assert got.accepted_pairs == want.accepted_pairs and got.out_information == want.out_information, (ring, mp_)
+        api.close_engines()
+    assert len(want.accepted_pairs) == 8 and (3, 34) in want.accepted_pairs          # the 30 static frames were skipped against anchor 3
+    assert api.end_process(frames[:1], timestamps_ms=stamps, config=cfg) == ([], [], [], [], [])
+    two = api.end_process(frames[:2], timestamps_ms=stamps, config=cfg, return_details=True)
+    assert two.accepted_pairs == [(0, 1)]
+    api.close_engines()
