@@ -138,7 +138,7 @@ def adaptive_histogram_equalization(noisy_arrs, *, clip_limit: float = 2.0, tile
         m = min(chunk, n - k)
         eng.upload(frames[k:k + m], first_slot=0)
         eng.clahe(0, m, clip_limit, tiles)
-        out[k:k + m] = eng.download(0, m)
+        eng.download(0, m, out=out[k:k + m])
     return out
 
 
@@ -163,7 +163,7 @@ def _denoise_frames(frames, windows, h, template_window, search_window, device, 
         eng.upload(frames[lo:hi], first_slot=0)
         tw = [windows[i] if k <= i < k + m else 0 for i in range(lo, hi)]       # halo frames are only read (window 0)
         eng.denoise(0, tw, h, template_window, search_window)
-        out[k:k + m] = eng.download(k - lo, m)
+        eng.download(k - lo, m, out=out[k:k + m])
     return out
 
 

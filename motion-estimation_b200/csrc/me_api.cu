@@ -973,9 +973,39 @@ int me_download(me_ctx *c, uint8_t *luma, size_t row_pitch, int first_slot, int 
     if (row_pitch < (size_t)c->W) return fail(ME_EINVAL, "row_pitch %zu < width %d", row_pitch, c->W);
     CU_TRY(cudaSetDevice(c->device));
     CU_TRY(cudaStreamSynchronize(c->s_copy));
-    CU_TRY(cudaMemcpy2D(luma, row_pitch, c->d_frames + (size_t)first_slot * c->frame_stride, c->pitch, (size_t)c->W,
-                        (size_t)n_frames * c->H, cudaMemcpyDeviceToHost));
-    return ME_OK;
+    cudaPointerAttributes pa;
+    const bool pinned = cudaPointerGetAttributes(&pa, luma) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+    if (!pinned) (void)cudaGetLastError();
+    const size_t frame_bytes = (size_t)c->W * c->H;
+    const int per_chunk = (int)(c->stage_bytes / frame_bytes);
+    if (pinned || per_chunk < 1) {                   // a page-locked destination takes the copy directly
+        CU_TRY(cudaMemcpy2D(luma, row_pitch, c->d_frames + (size_t)first_slot * c->frame_stride, c->pitch, (size_t)c->W,
+                            (size_t)n_frames * c->H, cudaMemcpyDeviceToHost));
+        return ME_OK;
+    }
+    // Pageable destination: device -> pinned staging (async, the fetch stream) while the chunk before it is copied from the
+    // other staging buffer into the caller's memory -- the mirror image of me_upload (a direct cudaMemcpy2D into pageable
+    // memory ran at a third of the link's rate: r02 bench, CLAHE end to end).
+    for (int sb = 0; sb < 2; ++sb) CU_TRY(cudaEventSynchronize(c->stage_free[sb]));      // no upload still reads the staging buffers
+    int pend_f = -1, pend_n = 0, pend_sb = 0;
+    auto drain = [&](int f, int nf, int sb) -> int {
+        CU_TRY(cudaEventSynchronize(c->stage_free[sb]));
+        uint8_t *dst = luma + (size_t)f * c->H * row_pitch;
+        if (row_pitch == (size_t)c->W) memcpy(dst, c->h_stage[sb], frame_bytes * nf);
+        else for (size_t r = 0; r < (size_t)nf * c->H; ++r) memcpy(dst + r * row_pitch, c->h_stage[sb] + r * c->W, (size_t)c->W);
+        return ME_OK;
+    };
+    for (int f = 0; f < n_frames; f += per_chunk) {
+        const int nf = n_frames - f < per_chunk ? n_frames - f : per_chunk;
+        const int sb = c->stage_next;
+        c->stage_next ^= 1;
+        CU_TRY(cudaMemcpy2DAsync(c->h_stage[sb], (size_t)c->W, c->d_frames + (size_t)(first_slot + f) * c->frame_stride, c->pitch,
+                                 (size_t)c->W, (size_t)nf * c->H, cudaMemcpyDeviceToHost, c->s_fetch));
+        CU_TRY(cudaEventRecord(c->stage_free[sb], c->s_fetch));
+        if (pend_f >= 0) { int rc = drain(pend_f, pend_n, pend_sb); if (rc) return rc; }
+        pend_f = f; pend_n = nf; pend_sb = sb;
+    }
+    return drain(pend_f, pend_n, pend_sb);
 }
 
 int me_copy_frames_device(me_ctx *c, void *d_dst, size_t dst_pitch, int first_slot, int n_frames, void *stream)

@@ -114,9 +114,13 @@ class MotionEstimator:
         check(self._L.me_denoise(self._ctx, int(first_slot), int(tw.size), tw.ctypes.data_as(C.POINTER(C.c_int32)),
                                  float(h), int(template_window), int(search_window)))
 
-    def download(self, first_slot=0, n_frames=1):
-        """Ring slots -> (n_frames,H,W) uint8 host array."""
-        out = np.empty((int(n_frames), self.height, self.width), np.uint8)
+    def download(self, first_slot=0, n_frames=1, out=None):
+        """Ring slots -> (n_frames,H,W) uint8 host array (into `out` when given: a C-contiguous-row view of that shape)."""
+        if out is None:
+            out = np.empty((int(n_frames), self.height, self.width), np.uint8)
+        elif (out.dtype != np.uint8 or out.shape != (int(n_frames), self.height, self.width) or out.strides[2] != 1
+              or out.strides[0] != self.height * out.strides[1]):
+            raise ValueError("out must be a (n_frames, H, W) uint8 array with contiguous pixels and evenly spaced rows")
         check(self._L.me_download(self._ctx, out.ctypes.data, out.strides[1], int(first_slot), int(n_frames)))
         return out
 
