@@ -39,7 +39,7 @@ __global__ void __launch_bounds__(256) clahe_lut_kernel(const ClaheArgs a, int f
 {
     // one histogram per warp: an eighth of the atomic contention (four copies per warp, by lane quarter, were tried and lost:
     // 68 -> 80 us, r02h -- the extra clearing and summing costs more than the same-address atomics it avoids)
-    __shared__ unsigned whist[8][256];
+    __shared__ __align__(1024) unsigned whist[8][256];          // 1 KB per warp, 1 KB aligned: bin address = base | (byte << 2)
     __shared__ unsigned wsum[8];
     __shared__ unsigned s_clipped;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -50,6 +50,12 @@ __global__ void __launch_bounds__(256) clahe_lut_kernel(const ClaheArgs a, int f
     if (tid == 0) s_clipped = 0;
     __syncthreads();
     const int xb = ti * a.tw, xe = xb + a.tw;             // the tile's columns; beyond W only in the reflect-extended case
+    const unsigned hbase = (unsigned)__cvta_generic_to_shared(&whist[warp][0]);
+    // one histogram update: shift the byte to bits 2..9, mask and merge the warp's base in one LOP3, one shared-memory reduction
+    auto bump = [&](uint32_t v, int q) {
+        const unsigned sh = q == 0 ? v << 2 : v >> (8 * q - 2);
+        asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(hbase | (sh & 0x3fcu)) : "memory");
+    };
     if (xe <= a.W) {
         // four pixels per load: aligned words that cover [xb, xe), bytes outside it masked off.  The tile's (row, word) pairs
         // are spread over the whole CTA and four loads are in flight per thread before the first histogram update (r02a ncu
@@ -59,35 +65,56 @@ __global__ void __launch_bounds__(256) clahe_lut_kernel(const ClaheArgs a, int f
         const int step_r = 256 / nw, step_c = 256 - step_r * nw;
         int r = tid / nw, cw = tid - r * nw;
         const bool inside = (tj + 1) * a.th <= a.H;                      // no reflected rows in this tile (all but a ragged last row of tiles)
-        for (int p0 = tid; p0 < total; p0 += 4 * 256) {
-            uint32_t v[4];
-            int wi[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                wi[u] = -1;
-                if (p0 + u * 256 < total) {
-                    wi[u] = w0 + cw;
-                    const int y = inside ? tj * a.th + r : reflect101(tj * a.th + r, a.H);
-                    v[u] = __ldg(reinterpret_cast<const uint32_t *>(f + (size_t)y * a.pitch) + wi[u]);
-                }
-                cw += step_c; r += step_r;
-                if (cw >= nw) { cw -= nw; ++r; }
-            }
-            if (((xb | xe) & 3) == 0) {                      // tile edges on word boundaries (the usual case): no per-byte tests
+        const bool aligned = ((xb | xe) & 3) == 0;                       // tile edges on word boundaries (the usual case): no per-byte tests
+        int p0 = tid;
+        if (inside && aligned) {
+            // the usual tile: byte offset of the thread's word kept incrementally (r02 SASS of the general loop: 28 instructions
+            // of address arithmetic and guards per load, 50 per word in all), no guards until the last partial round
+            unsigned off = (unsigned)(tj * a.th + r) * (unsigned)a.pitch + 4u * (unsigned)(w0 + cw);
+            const unsigned d_step = (unsigned)step_r * (unsigned)a.pitch + 4u * (unsigned)step_c;
+            const unsigned d_wrap = (unsigned)a.pitch - 4u * (unsigned)nw;
+            for (; p0 + 3 * 256 < total; p0 += 4 * 256) {
+                uint32_t v[4];
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
-                    if (wi[u] < 0) continue;
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) atomicAdd(&whist[warp][(v[u] >> (8 * q)) & 255u], 1u);
+                    v[u] = __ldg(reinterpret_cast<const uint32_t *>(f + off));
+                    off += d_step; cw += step_c;
+                    if (cw >= nw) { cw -= nw; off += d_wrap; }
                 }
-            } else {
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) bump(v[u], q);
+            }
+            for (; p0 < total; p0 += 256) {
+                const uint32_t v = __ldg(reinterpret_cast<const uint32_t *>(f + off));
+                off += d_step; cw += step_c;
+                if (cw >= nw) { cw -= nw; off += d_wrap; }
+#pragma unroll
+                for (int q = 0; q < 4; ++q) bump(v, q);
+            }
+        } else {
+            for (; p0 < total; p0 += 4 * 256) {
+                uint32_t v[4];
+                int wi[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    wi[u] = -1;
+                    if (p0 + u * 256 < total) {
+                        wi[u] = w0 + cw;
+                        const int y = inside ? tj * a.th + r : reflect101(tj * a.th + r, a.H);
+                        v[u] = __ldg(reinterpret_cast<const uint32_t *>(f + (size_t)y * a.pitch) + wi[u]);
+                    }
+                    cw += step_c; r += step_r;
+                    if (cw >= nw) { cw -= nw; ++r; }
+                }
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     if (wi[u] < 0) continue;
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         const int x = 4 * wi[u] + q;
-                        if (x >= xb && x < xe) atomicAdd(&whist[warp][(v[u] >> (8 * q)) & 255u], 1u);
+                        if (aligned || (x >= xb && x < xe)) bump(v[u], q);
                     }
                 }
             }

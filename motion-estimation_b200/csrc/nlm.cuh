@@ -13,8 +13,9 @@
 //   pass A  (row, 16-column segment) tasks: |a-b| of 4 pixels per VABSDIFF4, squares with IMAD, a sliding
 //           TWS-wide horizontal sum, 16 sums stored as 4 x STS.128; the words of the frame being denoised
 //           stay in registers for the whole kernel (they do not depend on the offset);
-//   pass B  one thread per (column, 32-row half): sliding TWS-high vertical sum of pass A's rows, weight
-//           lookup, est += w * pixel, wsum += w with the 64 accumulators in registers.
+//   pass B  one thread per (column, 32-row half): sliding TWS-high vertical sum of pass A's rows with the
+//           window's rows in registers (each sum is read once), weight lookup, est += w * pixel,
+//           wsum += w with the 64 accumulators in registers.
 // Integer-ALU/shared-memory bound: about 20 thread-instructions per output pixel per offset; HBM traffic
 // is the tile regions once per temporal frame (nothing per offset).
 #pragma once
@@ -79,6 +80,7 @@ __global__ void __launch_bounds__(kNlmThreads, 2) nlm_kernel(const NlmArgs a)
                   NTASK = NSEG * NR, ROUNDS = (NTASK + kNlmThreads - 1) / kNlmThreads, NPX = S + TWS - 1, NW = (NPX + 3) / 4,
                   HP = TW + 4;                                   // HP = 4 mod 32: conflict-free STS.128 from lanes on consecutive rows
     constexpr int SHIFT = nlm_shift(TWS);
+    static_assert(kNlmThreads == TW * (TR / K), "vertical pass: one thread per (column, K-row band)");
     extern __shared__ __align__(16) unsigned char nlm_smem[];
     int *s_h0 = reinterpret_cast<int *>(nlm_smem);              // 2 x (NR x HP) horizontal sums
     unsigned char *s_it = nlm_smem + 2 * NR * HP * 4;           // it_rows x itp displaced-frame region
@@ -120,16 +122,16 @@ __global__ void __launch_bounds__(kNlmThreads, 2) nlm_kernel(const NlmArgs a)
         }
     }
 
-    int est[K], wsum[K];                                        // [2 * i + column] of the thread's K/2 rows x 2 columns
+    int est[K], wsum[K];                                        // row i of the thread's column
 #pragma unroll
     for (int i = 0; i < K; ++i) est[i] = wsum[i] = 0;
 
     const int rows_all = T * sws;
     const int per = (rows_all + a.nsplit - 1) / a.nsplit;
     const int row_lo = sp * per, row_hi = min(rows_all, row_lo + per);
-    // vertical pass: a thread owns two adjacent columns (one 64-bit shared load serves both) and K/2 rows
-    constexpr int KB = K / 2;
-    const int j = (tid & (TW / 2 - 1)) * 2, rh = tid / (TW / 2);
+    // vertical pass: a thread owns one column and K rows; the TWS rows of its sliding window stay in registers, so every
+    // horizontal sum is read from shared memory once (K + TWS - 1 word loads per K outputs)
+    const int j = tid & (TW - 1), rh = tid / TW;
     if (LS) {
         for (int i = tid; i <= lut_n; i += kNlmThreads) s_lut[i] = (unsigned short)lut[i];
         // visible after the first __syncthreads below (the region staging)
@@ -174,31 +176,22 @@ __global__ void __launch_bounds__(kNlmThreads, 2) nlm_kernel(const NlmArgs a)
     };
     // ---- vertical pass of one offset from buffer `buf`: TWS-high sums, weights, accumulation
     auto pass_b = [&](int dy, int dx, int buf) {
-        const int *hp = s_h0 + buf * (NR * HP) + (rh * KB) * HP + j;
-        const unsigned char *pp = s_it + (rh * KB + b + dy) * itp + (j + b + dx);
-        int v0 = 0, v1 = 0;
+        const int *hp = s_h0 + buf * (NR * HP) + (rh * K) * HP + j;
+        const unsigned char *pp = s_it + (rh * K + b + dy) * itp + (j + b + dx);
+        int hw[TWS], v = 0;
 #pragma unroll
-        for (int r = 0; r < TWS; ++r) {
-            const int2 h2 = *reinterpret_cast<const int2 *>(hp + r * HP);
-            v0 += h2.x; v1 += h2.y;
-        }
+        for (int r = 0; r < TWS; ++r) { hw[r] = hp[r * HP]; v += hw[r]; }
 #pragma unroll
-        for (int i = 0; i < KB; ++i) {
-            int w0, w1;
-            if (LS) {
-                w0 = s_lut[min(v0 >> SHIFT, lut_n)];                 // clamped: the entry after the table is 0
-                w1 = s_lut[min(v1 >> SHIFT, lut_n)];
-            } else {
-                w0 = __ldg(lut + min(v0 >> SHIFT, lut_n));
-                w1 = __ldg(lut + min(v1 >> SHIFT, lut_n));
-            }
-            est[2 * i] += w0 * (int)pp[i * itp];
-            est[2 * i + 1] += w1 * (int)pp[i * itp + 1];
-            wsum[2 * i] += w0;
-            wsum[2 * i + 1] += w1;
-            if (i + 1 < KB) {
-                const int2 in = *reinterpret_cast<const int2 *>(hp + (i + TWS) * HP), out = *reinterpret_cast<const int2 *>(hp + i * HP);
-                v0 += in.x - out.x; v1 += in.y - out.y;
+        for (int i = 0; i < K; ++i) {
+            int w;
+            if (LS) w = s_lut[min(v >> SHIFT, lut_n)];               // clamped: the entry after the table is 0
+            else w = __ldg(lut + min(v >> SHIFT, lut_n));
+            est[i] += w * (int)pp[i * itp];
+            wsum[i] += w;
+            if (i + 1 < K) {
+                const int in = hp[(i + TWS) * HP];
+                v += in - hw[i % TWS];
+                hw[i % TWS] = in;
             }
         }
     };
@@ -234,7 +227,7 @@ __global__ void __launch_bounds__(kNlmThreads, 2) nlm_kernel(const NlmArgs a)
 
 #pragma unroll
     for (int i = 0; i < K; ++i) {
-        const int gy = y0 + rh * KB + (i >> 1), gx = x0 + j + (i & 1);
+        const int gy = y0 + rh * K + i, gx = x0 + j;
         if (gy >= a.H || gx >= a.W) continue;
         if (a.nsplit > 1) {
             int *acc = a.acc + (((long long)n * a.H + gy) * a.W + gx) * 2;
