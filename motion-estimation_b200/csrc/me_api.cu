@@ -197,7 +197,7 @@ struct me_ctx {
     int pstage_bytes = 0, smem_persistent = 0;    // resident kernel: one stage of window copies, total dynamic smem (0 = not usable)
     int *d_ready = nullptr, *d_error = nullptr;  // resident kernel: queue of completed pairs, wait-timeout flag
     size_t n_tile_tickets = 0;                    // entries of args.tile_ticket (slabbed plans only)
-    uint8_t *d_scan = nullptr;                    // me_anchored_scan on the device: [records max_frames | state 16 ints | barrier 2 words]
+    uint8_t *d_scan = nullptr;                    // me_anchored_scan on the device: [records max_frames | state 16 ints | barrier: arrivals, -, 64-bit word | trace]
     int64_t launches = 0;
     int64_t cand_px = 0, cand_px_valid = 0;
 };
@@ -1153,6 +1153,7 @@ int anchored_scan_device(me_ctx *c, int anchor_slot, int first_slot, int n_frame
 {
     *done = false;
     if (!c->kc.fn_scan || c->args.tmr != 1 || env_int("ME_SCAN_DEVICE", 1) == 0) return ME_OK;
+    if (c->max_frames >= (1 << me::kScanSlotBits)) return ME_OK;      // frame slots travel in 20-bit fields of the barrier word
     int coop = 0;
     CU_TRY(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->device));
     if (!coop) return ME_OK;
@@ -1176,11 +1177,16 @@ int anchored_scan_device(me_ctx *c, int anchor_slot, int first_slot, int n_frame
     sc.state = reinterpret_cast<int *>(c->d_scan + rec_bytes);
     sc.sync = reinterpret_cast<unsigned *>(c->d_scan + rec_bytes + 64);
     sc.trace = env_int("ME_SCAN_TRACE", 0) ? reinterpret_cast<unsigned long long *>(c->d_scan + rec_bytes + 96) : nullptr;
-    const long long most = (long long)a.tiles_per_pair * a.nsx * a.nsy * sc.max_look;      // units of the largest batch
+    sc.trace_cta = env_int("ME_SCAN_TRACE", 0) - 1;
     // every CTA of the grid arrives at every barrier, with or without work: no more CTAs per SM than ME_SCAN_CTAS (tuned: see DESIGN.md 4)
     const int cap = env_int("ME_SCAN_CTAS", 4);
     if (cap > 0 && per_sm > cap) per_sm = cap;
     long long grid = (long long)per_sm * c->sm_count;
+    // a batch that fits the grid is one unit per CTA; one pair more and a quarter of the CTAs run two while the rest wait (r02 trace,
+    // 640x64: 553 units on 444 CTAs), so the look-ahead stops where the grid is full -- when that still leaves a batch of two or more
+    const long long per_pair_units = (long long)a.tiles_per_pair * a.nsx * a.nsy;
+    if (env_int("ME_SCAN_FIT", 1) && grid / per_pair_units >= 2 && grid / per_pair_units < sc.max_look) sc.max_look = (int)(grid / per_pair_units);
+    const long long most = per_pair_units * sc.max_look;                                   // units of the largest batch
     if (grid > most) grid = most;
     CU_TRY(cudaMemsetAsync(c->d_scan + rec_bytes, 0, 256, st));
     void *params[4] = {(void *)&c->tm_win, (void *)&c->tm_ref, (void *)&a, (void *)&sc};
@@ -1199,13 +1205,19 @@ int anchored_scan_device(me_ctx *c, int anchor_slot, int first_slot, int n_frame
         return fail(ME_ECUDA, "the resident scan kernel gave up waiting at a grid barrier; the context has been reset");
     }
     if (sc.trace) {
-        unsigned long long tr[6];
+        unsigned long long tr[20];
         CU_TRY(cudaMemcpy(tr, sc.trace, sizeof tr, cudaMemcpyDeviceToHost));
         const double n = state[6] ? state[6] : 1;
         fprintf(stderr, "[me_b200] scan trace: %d steps (mean batch %.2f pairs), per step: CTA 0 %.2f us in search_tile + %.2f us at the barrier; "
-                "step start -> last CTA arrives %.2f us, the gate %.2f us (grid %lld x %d threads, %d units per pair)\n",
-                state[6], tr[5] / n, tr[0] * 1e-3 / n, tr[1] * 1e-3 / n, tr[2] * 1e-3 / n, tr[3] * 1e-3 / n, grid, c->threads,
+                "step start -> slowest unit has written its records %.2f us -> last CTA arrives %.2f us, the gate %.2f us (grid %lld x %d threads, %d units per pair)\n",
+                state[6], tr[5] / n, tr[0] * 1e-3 / n, tr[1] * 1e-3 / n, tr[7] * 1e-3 / n, tr[2] * 1e-3 / n, tr[3] * 1e-3 / n, grid, c->threads,
                 a.tiles_per_pair * a.nsx * a.nsy);
+        fprintf(stderr, "[me_b200] scan trace: CTA %d, SM-clock cycles per step: load %.0f, shifted copies %.0f, candidates %.0f, finalize %.0f, "
+                "ticket %.0f; pair reduction %.0f cycles each (%llu times)\n", sc.trace_cta, tr[8] / n, tr[9] / n, tr[10] / n, tr[11] / n,
+                tr[12] / n, tr[14] ? (double)tr[13] / (double)tr[14] : 0.0, tr[14]);
+        if (tr[14])
+            fprintf(stderr, "[me_b200] scan trace: inside a pair reduction: clear + key loads %.0f, sums %.0f, counting + selection %.0f, record %.0f cycles\n",
+                    (double)tr[15] / tr[14], (double)tr[16] / tr[14], (double)tr[17] / tr[14], (double)tr[18] / tr[14]);
     }
     if (searches) *searches = state[5];
     if (launches) *launches = state[6];

@@ -361,7 +361,9 @@ __device__ __forceinline__ void finalize_record(const SearchArgs &a, int pair, i
         a.blk_sad[b] = sad;
         reinterpret_cast<float2 *>(a.blk_sub)[b] = make_float2(fx, fy);
         a.blk_flags[b] = (uint8_t)flags;
-        __threadfence();
+        // no fence here: every caller synchronises its CTA (or warp) after the finalize loop and ONE thread then fences before it
+        // takes the pair's ticket -- fences are cumulative, so that one covers these stores (a fence per block was ~1 k cycles in
+        // front of every ticket: r02 scan trace)
     }
 }
 
@@ -406,7 +408,7 @@ __device__ __forceinline__ void finalize_block(const SearchArgs &a, int pair, co
 // the neighbour SADs come from the shifted copies with aligned word loads -- no global loads, no realignment,
 // no 64-bit address arithmetic (r01f ncu at +-8: the global-memory form was ~15 % of all issued instructions
 // and the source of the long-scoreboard stalls).  jr / jb: block row in the tile / block in the row.
-template <int B, int PITCH>
+template <int B, int PITCH, int FL = 8>
 __device__ __forceinline__ void finalize_block_smem(const SearchArgs &a, int pair, const uint8_t *s_win, const uint8_t *s_ref,
                                                     int jr, int jb, int bx, int by, uint32_t sad, uint32_t rank,
                                                     int lane, unsigned mask)
@@ -429,7 +431,7 @@ __device__ __forceinline__ void finalize_block_smem(const SearchArgs &a, int pai
     const uint32_t *cym = cand(ui, yin ? dyi - 1 : dyi), *cyp = cand(ui, yin ? dyi + 1 : dyi);
     uint32_t sxm = 0, sxp = 0, sym = 0, syp = 0, vmn = 0xffffffffu, vmx = 0u;
 #pragma unroll 2
-    for (int idx = lane; idx < B * SW; idx += kFinLanes) {
+    for (int idx = lane; idx < B * SW; idx += FL) {
         const int row = idx / SW, wd = idx - row * SW;
         const uint32_t rw = ref[row * RPW + wd];
         vmn = __vminu4(vmn, rw);
@@ -466,77 +468,146 @@ __device__ __forceinline__ void pair_keys(const uint8_t *fl, const float2 *sub, 
 }
 
 // Few blocks per pair (the 640x64 recordings have 160): the three radix passes, each clearing and scanning 2 x 2048 bins,
-// are a fixed ~10 us at the tail of every launch of the anchored scan, which waits for exactly that.  Here every thread
-// ranks its own keys by counting the smaller ones (ties by block index) in shared memory: one pass, two barriers.
+// are a fixed ~10 us at the tail of every launch of the anchored scan, which waits for exactly that.  Here the order
+// statistics come from counting: with lt(x) = #(valid keys < x), the m-th smallest key is max{x : lt(x) <= m} -- one compare
+// per key pair, no tie-break, and the selection is an atomicMax.  A (axis, block) key is counted by four adjacent lanes, a
+// quarter of the key list each (16-byte broadcast reads, four independent counters), joined by two shuffles.  The CTA that
+// runs this is the only busy one on its SM, one warp per scheduler: every dependent instruction costs its full latency, so
+// the instruction COUNT is what matters (r02 trace at 128 threads: first form, one thread per block and 14 instructions per
+// key, 14.7 k cycles per pair; lt and le counted separately and joined in shared memory, 10.4 k cycles in the counting alone).
 constexpr int kSmallNb = 512;
-static __device__ void reduce_pair_small(const SearchArgs &a, int pair, unsigned *scratch)
+static __device__ void reduce_pair_small(const SearchArgs &a, int pair, unsigned *scratch, unsigned long long *sub_phase = nullptr)
 {
-    uint32_t *kx = scratch, *ky = scratch + kSmallNb;
+    long long rc0 = sub_phase ? clock64() : 0;
+    int rci = 0;
+    auto rmark = [&]() {                         // trace only: cycles of [0] clear + key loads, [1] sums, [2] counting + selection, [3] record
+        if (sub_phase && threadIdx.x == 0) { const long long t = clock64(); atomicAdd(sub_phase + rci++, (unsigned long long)(t - rc0)); rc0 = t; }
+    };
+    uint32_t *kx = scratch;                      // [2][kSmallNb] keys, x then y; invalid = kNoKey = 0, below every real key
     unsigned *bc = scratch + 2 * kSmallNb;       // [0],[1] lower / upper middle key x; [2],[3] y; [4] textured; [5],[6] counts; [8..11] field sums
     const uint8_t *fl = a.blk_flags + (size_t)pair * a.nb;
     const float2 *sub = reinterpret_cast<const float2 *>(a.blk_sub) + (size_t)pair * a.nb;
     const int T = blockDim.x, tid = threadIdx.x, nb = a.nb;
+    const int nb16 = (nb + 15) & ~15;            // every quarter of the key list is whole 16-byte words: pad with kNoKey
     if (tid < 12) bc[tid] = 0;
+    for (int i = nb + tid; i < nb16; i += T) kx[i] = kx[kSmallNb + i] = kNoKey;
     __syncthreads();
     unsigned ntex = 0, nx = 0, ny = 0;
     long long fsx = 0, fsy = 0;
-    for (int b = tid; b < nb; b += T) {
-        uint32_t x, y;
-        unsigned tex;
-        float2 v;
-        pair_keys(fl, sub, b, x, y, tex, v);
-        kx[b] = x; ky[b] = y;
-        ntex += tex;
-        if (x != kNoKey) { ++nx; fsx += (long long)__float2ll_rn(__fmul_rn(v.x, 1048576.0f)); }
-        if (y != kNoKey) { ++ny; fsy += (long long)__float2ll_rn(__fmul_rn(v.y, 1048576.0f)); }
-    }
-    ntex = __reduce_add_sync(kFull, ntex); nx = __reduce_add_sync(kFull, nx); ny = __reduce_add_sync(kFull, ny);
+    for (int b0 = tid; b0 < nb; b0 += 2 * T) {   // two records in flight per thread (each is two dependent-free L2 reads)
+        uint32_t x[2], y[2];
+        unsigned tex[2];
+        float2 v[2];
 #pragma unroll
-    for (int o = 16; o; o >>= 1) {
-        fsx += __shfl_xor_sync(kFull, fsx, o);
-        fsy += __shfl_xor_sync(kFull, fsy, o);
+        for (int u = 0; u < 2; ++u) {
+            x[u] = y[u] = kNoKey; tex[u] = 0; v[u] = make_float2(0.f, 0.f);
+            if (b0 + u * T < nb) pair_keys(fl, sub, b0 + u * T, x[u], y[u], tex[u], v[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            if (b0 + u * T >= nb) continue;
+            kx[b0 + u * T] = x[u]; kx[kSmallNb + b0 + u * T] = y[u];
+            ntex += tex[u];
+            if (x[u] != kNoKey) { ++nx; fsx += (long long)__float2ll_rn(__fmul_rn(v[u].x, 1048576.0f)); }
+            if (y[u] != kNoKey) { ++ny; fsy += (long long)__float2ll_rn(__fmul_rn(v[u].y, 1048576.0f)); }
+        }
     }
+    rmark();
+    // warp sums: the 64-bit field sums as a low 16-bit and a high part (|v| <= 128.5 and at most four records per lane keep
+    // both inside 32 bits over a warp), one REDUX each instead of five 64-bit shuffle rounds
+    ntex = __reduce_add_sync(kFull, ntex); nx = __reduce_add_sync(kFull, nx); ny = __reduce_add_sync(kFull, ny);
+    const unsigned lox = __reduce_add_sync(kFull, (unsigned)(fsx & 0xffff)), loy = __reduce_add_sync(kFull, (unsigned)(fsy & 0xffff));
+    const int hix = __reduce_add_sync(kFull, (int)(fsx >> 16)), hiy = __reduce_add_sync(kFull, (int)(fsy >> 16));
     if ((tid & 31) == 0) {
+        const long long wx = (long long)hix * 65536 + (long long)lox, wy = (long long)hiy * 65536 + (long long)loy;
         if (ntex) atomicAdd(&bc[4], ntex);
         if (nx) atomicAdd(&bc[5], nx);
         if (ny) atomicAdd(&bc[6], ny);
-        if (fsx) atomicAdd(reinterpret_cast<unsigned long long *>(bc + 8), (unsigned long long)fsx);
-        if (fsy) atomicAdd(reinterpret_cast<unsigned long long *>(bc + 10), (unsigned long long)fsy);
+        if (wx) atomicAdd(reinterpret_cast<unsigned long long *>(bc + 8), (unsigned long long)wx);
+        if (wy) atomicAdd(reinterpret_cast<unsigned long long *>(bc + 10), (unsigned long long)wy);
     }
     __syncthreads();
+    rmark();
     const unsigned cx = bc[5], cy = bc[6];
-    for (int b = tid; b < nb; b += T) {
-        const uint32_t x = kx[b], y = ky[b];
-        unsigned rx = 0, ry = 0;
-        for (int j = 0; j < nb; ++j) {           // broadcast reads: every thread looks at the same j
-            const uint32_t xj = kx[j], yj = ky[j];
-            rx += (xj != kNoKey) & ((xj < x) | ((xj == x) & (j < b)));
-            ry += (yj != kNoKey) & ((yj < y) | ((yj == y) & (j < b)));
+    const int per = nb16 / 16, total = 8 * nb;                                   // 16-byte words per quarter; tasks = (axis, block, quarter)
+    uint32_t best[4] = {0u, 0u, 0u, 0u};                                         // running max of the keys with lt <= m: [2 * axis + (upper middle)]
+    for (int base = 0; base < total; base += T) {                                // uniform trip count: the shuffles below take whole warps
+        const int t = base + tid, idx = t >> 2, sq = t & 3;
+        const bool live = t < total;
+        const int axis = live && idx >= nb, blk = live ? idx - axis * nb : 0;
+        const uint32_t *k = kx + axis * kSmallNb;
+        const uint32_t x = k[blk];
+        const uint4 *k4 = reinterpret_cast<const uint4 *>(k) + sq * per;
+        unsigned c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+        // compare + predicated add, two instructions (the compiler's form of `c += kk < x` is three: compare, add, select)
+        auto lt1 = [&](unsigned &c, uint32_t kk) {
+            asm("{\n\t.reg .pred p;\n\tsetp.lt.u32 p, %1, %2;\n\t@p add.u32 %0, %0, 1;\n\t}" : "+r"(c) : "r"(kk), "r"(x));
+        };
+        auto count = [&](const uint4 kk) { lt1(c0, kk.x); lt1(c1, kk.y); lt1(c2, kk.z); lt1(c3, kk.w); };
+        int w = 0;
+        for (; w + 8 <= per; w += 8) {                                           // eight loads in flight: the loop is a chain of shared-memory latencies otherwise
+            uint4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = k4[w + u];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) count(v[u]);
         }
-        if (x != kNoKey) { if (rx == (cx - 1) / 2) bc[0] = x; if (rx == cx / 2) bc[1] = x; }
-        if (y != kNoKey) { if (ry == (cy - 1) / 2) bc[2] = y; if (ry == cy / 2) bc[3] = y; }
+        if (w + 4 <= per) {
+            const uint4 v0 = k4[w], v1 = k4[w + 1], v2 = k4[w + 2], v3 = k4[w + 3];
+            count(v0); count(v1); count(v2); count(v3);
+            w += 4;
+        }
+        if (w + 2 <= per) {
+            const uint4 v0 = k4[w], v1 = k4[w + 1];
+            count(v0); count(v1);
+            w += 2;
+        }
+        if (w < per) count(k4[w]);
+        unsigned lt = (c0 + c1) + (c2 + c3);
+        lt += __shfl_xor_sync(kFull, lt, 1);
+        lt += __shfl_xor_sync(kFull, lt, 2);
+        if (live && sq == 0 && x != kNoKey) {
+            const unsigned c = axis ? cy : cx;
+            lt -= (unsigned)nb16 - c;                                            // every invalid (and padding) key counted as smaller
+            const uint32_t lo = lt <= (c - 1) / 2 ? x : 0u, hi = lt <= c / 2 ? x : 0u;
+            if (axis) { best[2] = max(best[2], lo); best[3] = max(best[3], hi); }
+            else      { best[0] = max(best[0], lo); best[1] = max(best[1], hi); }
+        }
+    }
+    // half of all keys pass lt <= m: one shared-memory atomic per warp and target, not one per key (r02 trace: 320 same-address
+    // atomicMax made this loop 8.5 k cycles)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const uint32_t m = __reduce_max_sync(kFull, best[i]);
+        if ((tid & 31) == 0 && m) atomicMax(&bc[i], m);
     }
     __syncthreads();
+    rmark();
+    // the record: x fields by thread 0, y fields by the first thread of the next warp (two double divisions side by side)
+    me_pair_result *out = a.pair_out + pair;
+    const int ty = T >= 64 ? 32 : 0;
     if (tid == 0) {
-        me_pair_result r;
-        r.pdx = cx ? __fmul_rn(0.5f, __fadd_rn(funkey(bc[0]), funkey(bc[1]))) : 0.0f;
-        r.pdy = cy ? __fmul_rn(0.5f, __fadd_rn(funkey(bc[2]), funkey(bc[3]))) : 0.0f;
-        r.flag = (int)cx >= (a.min_valid > 1 ? a.min_valid : 1);
-        r.nvalid_x = (int)cx;
-        r.nvalid_y = (int)cy;
-        r.n_textured = (int)bc[4];
-        const long long sx = *reinterpret_cast<const long long *>(bc + 8), sy = *reinterpret_cast<const long long *>(bc + 10);
-        r.mean_dx = cx ? (float)__ddiv_rn((double)sx, __dmul_rn((double)cx, 1048576.0)) : 0.0f;
-        r.mean_dy = cy ? (float)__ddiv_rn((double)sy, __dmul_rn((double)cy, 1048576.0)) : 0.0f;
-        a.pair_out[pair] = r;
+        out->pdx = cx ? __fmul_rn(0.5f, __fadd_rn(funkey(bc[0]), funkey(bc[1]))) : 0.0f;
+        out->flag = (int)cx >= (a.min_valid > 1 ? a.min_valid : 1);
+        out->nvalid_x = (int)cx;
+        out->n_textured = (int)bc[4];
+        const long long sx = *reinterpret_cast<const long long *>(bc + 8);
+        out->mean_dx = cx ? (float)__ddiv_rn((double)sx, __dmul_rn((double)cx, 1048576.0)) : 0.0f;
         a.pair_ticket[pair] = 0;                    // leave the scratch clean for the next launch
     }
+    if (tid == ty) {
+        out->pdy = cy ? __fmul_rn(0.5f, __fadd_rn(funkey(bc[2]), funkey(bc[3]))) : 0.0f;
+        out->nvalid_y = (int)cy;
+        const long long sy = *reinterpret_cast<const long long *>(bc + 10);
+        out->mean_dy = cy ? (float)__ddiv_rn((double)sy, __dmul_rn((double)cy, 1048576.0)) : 0.0f;
+    }
+    rmark();
 }
 
 // scratch: the CTA's shared memory from offset 0 (at least 2*kSelBins*4 + 128 bytes)
-static __device__ void reduce_pair(const SearchArgs &a, int pair, unsigned *scratch)
+static __device__ void reduce_pair(const SearchArgs &a, int pair, unsigned *scratch, unsigned long long *sub_phase = nullptr)
 {
-    if (a.nb <= kSmallNb) { reduce_pair_small(a, pair, scratch); return; }     // uniform across the CTA
+    if (a.nb <= kSmallNb) { reduce_pair_small(a, pair, scratch, sub_phase); return; }     // uniform across the CTA
     unsigned *hist = scratch;                    // [2][kSelBins]
     unsigned *bc = scratch + 2 * kSelBins;       // per axis: [0] chosen bin, [1] rank inside it, [2] its count, [3] total; [8],[9] next keys; [10] textured; [12..15] field sums
     const uint8_t *fl = a.blk_flags + (size_t)pair * a.nb;
@@ -776,10 +847,34 @@ __device__ __forceinline__ void run_item(const SearchArgs &a, bool active, int j
 constexpr bool kSliceMR = true;               // multi-row tiles (small ranges): 16-row patches as two rolled 8-row slices
 // search_tile: everything one CTA does for one unit (tile x candidate slab) -- the body of sad_search_kernel, and of every
 // iteration of sad_scan_kernel (sad_scan.cuh), which walks units in a loop.  `smem` is the CTA's dynamic shared memory.
-template <int B, int NDY, int NQ, int PITCH, bool K64, int RB, bool MR>
+// SCAN: the build inside sad_scan_kernel, where one unit's latency is what counts: the pair's frame slots come from the caller
+// (the barrier word) instead of the pair list, a tile with few blocks is finalized by a whole warp per block, and under
+// ME_SCAN_TRACE thread 0 adds the SM-clock cycles of each phase to phase[0..5] (load, shifted copies, candidates, finalize,
+// ticket, pair reduction) when `phase` is not null.
+struct TileTrace {
+    unsigned long long *phase;       // the traced CTA only: cycle sums per phase
+    unsigned long long *unit_max;    // every CTA: atomicMax of (records written - t_step) in ns, the step's slowest unit
+    unsigned long long *reduce;      // every CTA that reduces a pair: [0] cycles, [1] how often, [2..5] reduce_pair_small's parts
+    unsigned long long t_step;       // globaltimer when this CTA began the step
+};
+template <int B, int NDY, int NQ, int PITCH, bool K64, int RB, bool MR, bool SCAN = false>
 __device__ __forceinline__ void search_tile(const CUtensorMap &tm_win, const CUtensorMap &tm_ref, const SearchArgs &a, const int unit,
-                                            uint8_t *smem)
+                                            uint8_t *smem, const TileTrace *trace = nullptr, int scan_prev = 0, int scan_cur = 0)
 {
+    constexpr bool TRC = SCAN;
+    unsigned long long *phase = TRC && trace ? trace->phase : nullptr;
+    long long tc0 = 0;
+    int tci = 0;
+    auto mark = [&]() {
+        if constexpr (TRC) {
+            if (phase && threadIdx.x == 0) {
+                const long long t = clock64();
+                phase[tci++] += (unsigned long long)(t - tc0);
+                tc0 = t;
+            }
+        }
+    };
+    if constexpr (TRC) { if (phase && threadIdx.x == 0) tc0 = clock64(); }
     using KeyT = typename KeyOf<K64>::T;
     using G = Geo<B>;
     constexpr KeyT kNone = ~KeyT(0);
@@ -795,7 +890,7 @@ __device__ __forceinline__ void search_tile(const CUtensorMap &tm_win, const CUt
     const int ubase = sx * a.su, dbase = a.dy0 + sy * a.sd;
     const int lastx = sx == a.nsx - 1;
     const int slab_w = lastx ? a.U - ubase : a.su, slab_h = (sy == a.nsy - 1) ? a.dy0 + a.Uy - dbase : a.sd;
-    const int prev_slot = __ldcg(a.pairs + 2 * pair), cur_slot = __ldcg(a.pairs + 2 * pair + 1);   // L2: the scan kernel rewrites the list
+    const int prev_slot = SCAN ? scan_prev : __ldg(a.pairs + 2 * pair), cur_slot = SCAN ? scan_cur : __ldg(a.pairs + 2 * pair + 1);
     const int tmr = MR ? a.tmr : 1;
     const int X0 = tx * a.tmb * G::MB, Y0 = ty * tmr * B;
     const int nj = min(a.tmb, a.nmbx - tx * a.tmb);                    // macro-blocks in a row of this tile
@@ -864,6 +959,7 @@ __device__ __forceinline__ void search_tile(const CUtensorMap &tm_win, const CUt
         __syncthreads();
     }
 
+    mark();                                                            // [0] pair list + TMA
     // ---- derive the byte-shifted copies
     if (nd > 0) {
         build_shifted_copies<PITCH>(a, s_raw, s_win, tid, (int)blockDim.x);
@@ -871,6 +967,7 @@ __device__ __forceinline__ void search_tile(const CUtensorMap &tm_win, const CUt
         if (a.use_tma && tid == 0) mbar_inval(s_bar);                  // the scan kernel initialises it again for its next unit
     }
 
+    mark();                                                            // [1] shifted copies
     // ---- candidate patches.  The magic numbers of the usual case come precomputed from the host: a
     //      64-bit division per warp and CTA showed up as 10 ALU instructions per work item in r01c.
     const int lasty = sy == a.nsy - 1;
@@ -940,6 +1037,7 @@ __device__ __forceinline__ void search_tile(const CUtensorMap &tm_win, const CUt
     }
     }
     __syncthreads();
+    mark();                                                            // [2] candidates
 
     // ---- several slabs per tile: fold this CTA's block minima into the global keys; the CTA that
     //      arrives last at the tile's ticket owns the finalize step.
@@ -971,6 +1069,14 @@ __device__ __forceinline__ void search_tile(const CUtensorMap &tm_win, const CUt
         constexpr KeyT rmask = (KeyT(1) << RB) - 1;
         constexpr int per_warp = 32 / kFinLanes;
         const int grp = lane / kFinLanes;
+        if (SCAN && nslab == 1 && nblk * nrows <= nwarps) {            // few blocks: a whole warp per block, a quarter of the passes
+            if (warp < nblk * nrows) {
+                const int jr = MR ? warp / nblk : 0, jb = warp - jr * nblk;
+                const KeyT key = s_key[jr * a.tmb * G::NSUB + jb];
+                finalize_block_smem<B, PITCH, 32>(a, pair, s_win, s_ref, jr, jb, tx * a.tmb * G::NSUB + jb, ty * tmr + jr,
+                                                  (uint32_t)(key >> RB), (uint32_t)(key & rmask), lane, 0xffffffffu);
+            }
+        } else
         for (int jt = warp * per_warp + grp; jt < nblk * nrows; jt += nwarps * per_warp) {
             const int jr = MR ? jt / nblk : 0, jb = jt - jr * nblk;    // block row in the tile, block in the row
             const KeyT key = s_key[jr * a.tmb * G::NSUB + jb];
@@ -984,17 +1090,35 @@ __device__ __forceinline__ void search_tile(const CUtensorMap &tm_win, const CUt
         }
     }
     __syncthreads();
+    mark();                                                            // [3] finalize
+    if constexpr (TRC) {
+        if (trace && trace->unit_max && threadIdx.x == 0) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            atomicMax(trace->unit_max, t - trace->t_step);
+        }
+    }
 
-    // ---- ticket: the last CTA of this pair reduces it
+    // ---- ticket: the last CTA of this pair reduces it.  Thread 0 fences on both sides of its ticket (release: the CTA's
+    //      records, ordered before it by the barrier above; acquire: the other CTAs' records, read through L2 by all threads
+    //      after the barrier below) -- fences are cumulative, so the other threads need none (128 fences were ~2 k cycles)
     if (tid == 0) {
         __threadfence();
         const unsigned old = atomicAdd(&a.pair_ticket[pair], 1u);
-        *s_last = (old == (unsigned)a.tiles_per_pair - 1u);
+        const bool last = old == (unsigned)a.tiles_per_pair - 1u;
+        if (last) __threadfence();
+        *s_last = last;
     }
     __syncthreads();
+    mark();                                                            // [4] ticket
     if (*s_last) {
-        __threadfence();
-        reduce_pair(a, pair, reinterpret_cast<unsigned *>(smem));
+        long long tr0 = 0;
+        if constexpr (TRC) { if (trace && tid == 0) tr0 = clock64(); }
+        reduce_pair(a, pair, reinterpret_cast<unsigned *>(smem), TRC && trace ? trace->reduce + 2 : nullptr);
+        if constexpr (TRC) {
+            __syncthreads();
+            if (trace && tid == 0) { atomicAdd(trace->reduce, (unsigned long long)(clock64() - tr0)); atomicAdd(trace->reduce + 1, 1ull); }
+        }
     }
 }
 
