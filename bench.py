@@ -251,22 +251,50 @@ def run_search(args, rk, wl):
         kernel_ms.append(est.last_search_ms())
 
     # ---- e2e: host frames in, host records out, every step (pinned host -> device inside the region, overlapped)
+    # (measured at N = 1, 10 steps: 1080p 8.575 -> 8.422 ms per step with the first step in four slices; the 512-pair recording of the
+    # strong-scaling workload did not gain -- 68.0 -> 68.5 ms -- and keeps its first step whole)
+    parts = max(1, min(int(os.environ.get("ME_BENCH_FILL_PARTS", "1" if strong else "4")), P))
+    cut = [P * i // parts for i in range(parts + 1)]
+
+    def first_step():
+        """Step 0 in `parts` slices -- the search of a slice starts when ITS frames are on the device, so the pipeline fills after
+        a quarter of an upload instead of a whole one.  Returns (ticket, pairs) of every slice (no gather)."""
+        tickets = []
+        for i in range(parts):
+            a, b = cut[i], cut[i + 1]
+            lo = 0 if i == 0 else a + 1
+            est.upload(host_frames[lo:b + 1], first_slot=lo)
+            est.launch(half[0][a:b])
+            if gather:
+                gather.stage(est, b - a, offset=a)
+            else:
+                tickets.append((est.last_ticket(), b - a))
+        return tickets
+
     def e2e_steps(n):
-        est.upload(host_frames, first_slot=0)
-        out, prev = None, None
+        out, prev, head = None, None, []
         for s in range(n):
-            est.launch(half[s & 1])
+            if s == 0:
+                tickets = first_step()
+            else:
+                est.launch(half[s & 1])
             est.upload(host_frames, first_slot=(P + 1) * ((s + 1) & 1))     # next step's input, overlaps this search
             if gather:
-                ticket = gather.start(est, P)
+                ticket = gather.start(est, 0 if s == 0 else P)              # step 0's records were staged slice by slice
                 if prev is not None:
                     out = gather.wait(prev, counts)
             else:
                 ticket = est.last_ticket()
+                if s == 0:                                                   # the record ring holds four searches: take the early slices now
+                    head = [est.fetch_pairs(m, ticket=t) for t, m in tickets[:-1]]
                 if prev is not None:
-                    out = est.fetch_pairs(P, ticket=prev)                    # step k-1's records while step k searches: no idle gap
+                    tail = est.fetch_pairs(P if s > 1 else cut[-1] - cut[-2], ticket=prev)   # step k-1's records while step k searches
+                    out = np.concatenate(head + [tail]) if s == 1 else tail
             prev = ticket
-        return gather.wait(prev, counts) if gather else est.fetch_pairs(P, ticket=prev)
+        if gather:
+            return gather.wait(prev, counts)
+        tail = est.fetch_pairs(P if n > 1 else cut[-1] - cut[-2], ticket=prev)
+        return np.concatenate(head + [tail]) if n == 1 else tail
 
     e2e_steps(max(args.warmup, 2))
     rk.barrier()

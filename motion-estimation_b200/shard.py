@@ -117,6 +117,13 @@ class RecordGather:
         self.done = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
         self.k = 0
 
+    def stage(self, est, n_pairs, offset=0):
+        """Copy the records of est's last search to send[offset : offset + n_pairs] of the buffer the next start() gathers
+        (a step searched in several launches stages each of them; start(est, 0) then gathers what was staged)."""
+        if n_pairs:
+            b = self.k & 1
+            est.copy_pair_records_device(self.send[b][offset:].data_ptr(), n_pairs, stream=self.side.cuda_stream)
+
     def start(self, est, n_pairs):
         """Queue the gather of the records of est's last search; returns a ticket for wait()."""
         b = self.k & 1
