@@ -529,49 +529,75 @@ static __device__ void reduce_pair_small(const SearchArgs &a, int pair, unsigned
     __syncthreads();
     rmark();
     const unsigned cx = bc[5], cy = bc[6];
-    const int per = nb16 / 16, total = 8 * nb;                                   // 16-byte words per quarter; tasks = (axis, block, quarter)
+    const int per = nb16 / 16;                                                   // 16-byte words per quarter of a key list
     uint32_t best[4] = {0u, 0u, 0u, 0u};                                         // running max of the keys with lt <= m: [2 * axis + (upper middle)]
-    for (int base = 0; base < total; base += T) {                                // uniform trip count: the shuffles below take whole warps
-        const int t = base + tid, idx = t >> 2, sq = t & 3;
-        const bool live = t < total;
-        const int axis = live && idx >= nb, blk = live ? idx - axis * nb : 0;
+    // compare + predicated add, two instructions (the compiler's form of `c += kk < x` is three: compare, add, select)
+    auto lt1 = [](unsigned &c, uint32_t kk, uint32_t x) {
+        asm("{\n\t.reg .pred p;\n\tsetp.lt.u32 p, %1, %2;\n\t@p add.u32 %0, %0, 1;\n\t}" : "+r"(c) : "r"(kk), "r"(x));
+    };
+    constexpr int kRegWords = 10;                                                // 160 keys per axis: the recordings
+    if (per <= kRegWords) {
+        // A lane's role is fixed -- axis (tid >> 2) & 1, quarter tid & 3 -- so its quarter of the keys sits in registers for the whole
+        // loop, and a group of eight lanes (both axes, four quarters) takes two blocks per round: a round is one key read per
+        // block, the compares, and two shuffles; no shared-memory traffic in between (r02 trace: rounds that re-read the keys from
+        // shared memory cost ~790 cycles each at one warp per scheduler, twice what their instruction count explains).
+        const int axis = (tid >> 2) & 1, sq = tid & 3, grp = tid >> 3, ngrp = T >> 3;
         const uint32_t *k = kx + axis * kSmallNb;
-        const uint32_t x = k[blk];
         const uint4 *k4 = reinterpret_cast<const uint4 *>(k) + sq * per;
-        unsigned c0 = 0, c1 = 0, c2 = 0, c3 = 0;
-        // compare + predicated add, two instructions (the compiler's form of `c += kk < x` is three: compare, add, select)
-        auto lt1 = [&](unsigned &c, uint32_t kk) {
-            asm("{\n\t.reg .pred p;\n\tsetp.lt.u32 p, %1, %2;\n\t@p add.u32 %0, %0, 1;\n\t}" : "+r"(c) : "r"(kk), "r"(x));
-        };
-        auto count = [&](const uint4 kk) { lt1(c0, kk.x); lt1(c1, kk.y); lt1(c2, kk.z); lt1(c3, kk.w); };
-        int w = 0;
-        for (; w + 8 <= per; w += 8) {                                           // eight loads in flight: the loop is a chain of shared-memory latencies otherwise
-            uint4 v[8];
+        uint4 kr[kRegWords];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) v[u] = k4[w + u];
+        for (int u = 0; u < kRegWords; ++u) kr[u] = u < per ? k4[u] : make_uint4(~0u, ~0u, ~0u, ~0u);   // padding is never below a key
+        const unsigned c = axis ? cy : cx, inval = (unsigned)nb16 - c, m1 = (c - 1) / 2, m2 = c / 2;
+        uint32_t bl = 0u, bh = 0u;
+        for (int base = 0; base < nb; base += 2 * ngrp) {                        // uniform trip count: the shuffles take whole warps
+            const int ba = base + grp, bb = base + ngrp + grp;
+            const uint32_t xa = ba < nb ? k[ba] : kNoKey, xb = bb < nb ? k[bb] : kNoKey;
+            unsigned a0 = 0, a1 = 0, a2 = 0, a3 = 0, b0 = 0, b1 = 0, b2 = 0, b3 = 0;
 #pragma unroll
-            for (int u = 0; u < 8; ++u) count(v[u]);
+            for (int u = 0; u < kRegWords; ++u) {
+                lt1(a0, kr[u].x, xa); lt1(a1, kr[u].y, xa); lt1(a2, kr[u].z, xa); lt1(a3, kr[u].w, xa);
+                lt1(b0, kr[u].x, xb); lt1(b1, kr[u].y, xb); lt1(b2, kr[u].z, xb); lt1(b3, kr[u].w, xb);
+            }
+            unsigned lta = (a0 + a1) + (a2 + a3), ltb = (b0 + b1) + (b2 + b3);
+            lta += __shfl_xor_sync(kFull, lta, 1); ltb += __shfl_xor_sync(kFull, ltb, 1);
+            lta += __shfl_xor_sync(kFull, lta, 2); ltb += __shfl_xor_sync(kFull, ltb, 2);
+            if (sq == 0) {
+                lta -= inval; ltb -= inval;                                      // every invalid (and padding-0) key counted as smaller
+                if (xa != kNoKey) { if (lta <= m1) bl = max(bl, xa); if (lta <= m2) bh = max(bh, xa); }
+                if (xb != kNoKey) { if (ltb <= m1) bl = max(bl, xb); if (ltb <= m2) bh = max(bh, xb); }
+            }
         }
-        if (w + 4 <= per) {
-            const uint4 v0 = k4[w], v1 = k4[w + 1], v2 = k4[w + 2], v3 = k4[w + 3];
-            count(v0); count(v1); count(v2); count(v3);
-            w += 4;
-        }
-        if (w + 2 <= per) {
-            const uint4 v0 = k4[w], v1 = k4[w + 1];
-            count(v0); count(v1);
-            w += 2;
-        }
-        if (w < per) count(k4[w]);
-        unsigned lt = (c0 + c1) + (c2 + c3);
-        lt += __shfl_xor_sync(kFull, lt, 1);
-        lt += __shfl_xor_sync(kFull, lt, 2);
-        if (live && sq == 0 && x != kNoKey) {
-            const unsigned c = axis ? cy : cx;
-            lt -= (unsigned)nb16 - c;                                            // every invalid (and padding) key counted as smaller
-            const uint32_t lo = lt <= (c - 1) / 2 ? x : 0u, hi = lt <= c / 2 ? x : 0u;
-            if (axis) { best[2] = max(best[2], lo); best[3] = max(best[3], hi); }
-            else      { best[0] = max(best[0], lo); best[1] = max(best[1], hi); }
+        best[0] = axis ? 0u : bl; best[1] = axis ? 0u : bh; best[2] = axis ? bl : 0u; best[3] = axis ? bh : 0u;
+    } else {
+        const int total = 8 * nb;                                                // tasks = (axis, block, quarter)
+        for (int base = 0; base < total; base += T) {                            // uniform trip count: the shuffles below take whole warps
+            const int t = base + tid, idx = t >> 2, sq = t & 3;
+            const bool live = t < total;
+            const int axis = live && idx >= nb, blk = live ? idx - axis * nb : 0;
+            const uint32_t *k = kx + axis * kSmallNb;
+            const uint32_t x = k[blk];
+            const uint4 *k4 = reinterpret_cast<const uint4 *>(k) + sq * per;
+            unsigned c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+            auto count = [&](const uint4 kk) { lt1(c0, kk.x, x); lt1(c1, kk.y, x); lt1(c2, kk.z, x); lt1(c3, kk.w, x); };
+            int w = 0;
+            for (; w + 8 <= per; w += 8) {                                       // eight loads in flight
+                uint4 v[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) v[u] = k4[w + u];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) count(v[u]);
+            }
+            for (; w < per; ++w) count(k4[w]);
+            unsigned lt = (c0 + c1) + (c2 + c3);
+            lt += __shfl_xor_sync(kFull, lt, 1);
+            lt += __shfl_xor_sync(kFull, lt, 2);
+            if (live && sq == 0 && x != kNoKey) {
+                const unsigned c = axis ? cy : cx;
+                lt -= (unsigned)nb16 - c;                                        // every invalid (and padding) key counted as smaller
+                const uint32_t lo = lt <= (c - 1) / 2 ? x : 0u, hi = lt <= c / 2 ? x : 0u;
+                if (axis) { best[2] = max(best[2], lo); best[3] = max(best[3], hi); }
+                else      { best[0] = max(best[0], lo); best[1] = max(best[1], hi); }
+            }
         }
     }
     // half of all keys pass lt <= m: one shared-memory atomic per warp and target, not one per key (r02 trace: 320 same-address
