@@ -22,7 +22,9 @@ Workloads (one JSON line each; `config.workload` names it):
 
 Every line carries: value (inputs resident in HBM, device-timed with CUDA events, max over ranks), e2e (host buffers in,
 host results out, copies inside the timed region), roofline for the dominant kernel, cpu_baseline (a bounded sample on the
-host cores, rank 0, N = 1 only), clocks sampled during the timed region, gpu_launches.
+host cores, rank 0, N = 1 only), clocks sampled during the timed region, gpu_launches.  The e2e arm of the search workloads
+uploads step k+1 while step k searches; its first step goes in four slices (ME_BENCH_FILL_PARTS) so that the search starts
+after a quarter of an upload.
 
 The reference arm runs the reference's own CPU code for the workload (its pyramid ECC per pair, restated in
 oracle/ecc_port.py because /root/reference is Python and does not travel; cv2's CLAHE / fastNlMeansDenoisingMulti for

@@ -153,3 +153,33 @@ def test_end_process_static_stretch_longer_than_the_device_window(me):
     two = api.end_process(frames[:2], timestamps_ms=stamps, config=cfg, return_details=True)
     assert two.accepted_pairs == [(0, 1)]
     api.close_engines()
+
+
+@pytest.mark.parametrize("range_y", [0, 8])
+def test_anchor_walk_drivers_agree(me, monkeypatch, range_y):
+    """me_anchored_scan: the resident scan kernel (look-ahead fitted to the grid, and not) and the host-driven loop inside the
+    library return the same bytes -- the batches differ, the records may not -- and the first pair's record is the oracle's."""
+    from motion_estimation_b200 import synth
+    H, W, n = 64, 640, 150
+    canvas = synth.texture(H + 8, W + 3 * n + 40, seed=21)
+    steps = np.random.default_rng(5).choice([0, 1, 2, 3, 5], size=n)             # slow stretches (several skips in a row) and fast ones
+    offs = np.cumsum(steps)
+    frames = np.stack([canvas[4:4 + H, 3 * n + 20 - o: 3 * n + 20 - o + W] for o in offs])
+    cfg = me.SearchConfig(16, 64, range_y=range_y, min_range=6)
+    with me.MotionEstimator(H, W, cfg, max_frames=n + 1, max_pairs=16) as est:
+        est.upload(frames, first_slot=1)
+        runs = {}
+        for name, env in (("device", {}), ("device, look-ahead not fitted", {"ME_SCAN_FIT": "0"}), ("host loop", {"ME_SCAN_DEVICE": "0"})):
+            for k, v in env.items():
+                monkeypatch.setenv(k, v)
+            rec, searches, launches = est.anchored_scan(1, 2, n - 1)
+            for k in env:
+                monkeypatch.delenv(k)
+            runs[name] = rec.tobytes()
+            assert searches >= n - 1 and 1 <= launches <= searches
+        first = np.frombuffer(runs["device"], dtype=rec.dtype)
+        assert int(first["accepted"].sum()) > 10 and int((first["accepted"] == 0).sum()) > 10
+        for name in runs:
+            assert runs[name] == runs["device"], name
+        o = osad.search(frames[0], frames[1], 16, 64, range_y=range_y, min_range=6)
+        assert first["pair"]["pdx"][0] == np.float32(o["pdx"]) and first["pair"]["flag"][0] == o["flag"]
