@@ -401,8 +401,9 @@ def run_sweep(args, rk):
         pinned = torch.empty(mine.shape, dtype=torch.uint8, pin_memory=True)
         pinned.numpy()[:] = mine
         pairs = [(2 * i, 2 * i + 1) for i in range(P)]
+        halves = [pairs, [(2 * P + a, 2 * P + b) for a, b in pairs]]       # two sets of ring slots: step k+1 is uploaded while step k searches
         for R in (8, 16, 32, 64, 128):
-            est = me.MotionEstimator(H, W, me.SearchConfig(B, R), max_frames=2 * P, max_pairs=P, device=rk.local)
+            est = me.MotionEstimator(H, W, me.SearchConfig(B, R), max_frames=4 * P, max_pairs=P, device=rk.local)
             est.upload(pinned.numpy())
             for _ in range(3):
                 est.launch(pairs)
@@ -423,14 +424,19 @@ def run_sweep(args, rk):
             good = (not exact) or bool(np.all(np.rint(rec["pdx"]) == shifts[2 * lo:2 * hi:2, 0]))
             rk.barrier()
             t0 = time.perf_counter()
-            for _ in range(steps):                                          # e2e: host frames in, host records out
-                est.upload(pinned.numpy())
-                est.launch(pairs)
-                if gather:
-                    gather.wait(gather.start(est, P))
-                else:
-                    est.fetch_pairs(P)
+            est.upload(pinned.numpy(), first_slot=0)                        # e2e: host frames in, host records out, every step
+            prev, e2e_rec = None, None
+            for s in range(steps):
+                est.launch(halves[s & 1])
+                est.upload(pinned.numpy(), first_slot=2 * P * ((s + 1) & 1))    # the next step's frames, while this one searches
+                ticket = gather.start(est, P) if gather else est.last_ticket()
+                if prev is not None:
+                    e2e_rec = gather.wait(prev) if gather else est.fetch_pairs(P, ticket=prev)
+                prev = ticket
+            e2e_rec = gather.wait(prev) if gather else est.fetch_pairs(P, ticket=prev)
             e2e_s = rk.max(time.perf_counter() - t0) / steps
+            if not gather:
+                good = good and bool(np.array_equal(e2e_rec["pdx"], rec["pdx"]))
             ms = rk.max(ms)
             geo = est.geometry
             work = geo["cand_px_per_pair_valid"] * P
