@@ -957,6 +957,9 @@ __device__ __forceinline__ void search_tile(const CUtensorMap &tm_win, const CUt
         if (tid == 0) mbar_init(s_bar, 1);
         __syncthreads();
         if (tid == 0) {
+            // the scan kernel reuses this shared memory unit after unit: the generic-proxy stores of the unit before (shifted copies,
+            // reduction scratch; ordered before this point by the barrier) come before the async-proxy writes of the loads below
+            if constexpr (SCAN) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             const uint32_t bytes = (uint32_t)a.n_row_boxes * a.box_rows * PITCH + (uint32_t)ref_bytes;
             mbar_expect_tx(s_bar, bytes);
             for (int rb = 0; rb < a.n_row_boxes; ++rb)
