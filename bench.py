@@ -45,6 +45,7 @@ if ROOT not in sys.path:
 
 PIXELS_PER_MM, FRAME_DT_MS = 611.0, 5.531
 WORKLOADS = ("1080p", "strong", "4k", "sweep64", "clip", "nlm", "clahe")
+NCU_DRAM_BYTES_1080P = 137510656 + 8808704      # profiles/r02_1080p_ncu_summary.txt: sad_search_persistent<16,5,4,208>, 64 pairs of 1080p
 SEARCH_SHAPES = {   # workload -> (H, W, block, range, pairs per step per GPU)
     "1080p": (1080, 1920, 16, 32, 64),
     "strong": (1080, 1920, 16, 32, 512),
@@ -326,8 +327,11 @@ def run_search(args, rk, wl):
     kname = "sad_search_persistent" if geo.get("resident_kernel") else "sad_search_kernel"
     roofline = {
         "bound": "int_alu", "kernel": f"{kname}<{B},5,4,{geo['window_pitch']}>", "achieved": achieved / 1e9, "peak": peak_alu / 1e9,
-        "unit": "Gcand*px/s", "frac": achieved / peak_alu, "traffic": None,
-        "traffic_note": "DRAM bytes per launch are measured with ncu --set full, not in this run: profiles/r02_*_ncu_summary.txt",
+        "unit": "Gcand*px/s", "frac": achieved / peak_alu,
+        # dram__bytes_read.sum + dram__bytes_write.sum of one launch of this kernel on this workload, from the committed ncu --set full
+        # capture (137.51 + 8.81 MB against 143.5 MB algorithmic: frames read once, records written once); other shapes: not captured
+        "traffic": NCU_DRAM_BYTES_1080P if (wl == "1080p" and P == 64 and geo.get("resident_kernel")) else None,
+        "traffic_note": "from profiles/r02_1080p_ncu_summary.txt (ncu --set full of the same kernel and step, a separate run)",
         "peak_is": f"{sms} SMs x {ipc:.2f} VABSDIFF4 thread-instr/clk/SM (this repo's microbenchmark, run here; MEASURED_PEAKS.json "
                    f"has no integer-ALU entry) x 4 px x {f_max / 1e6:.0f} MHz max SM clock; {peak_src}",
         "frac_at_observed_clock": achieved / (sms * ipc * 4.0 * (clocks["sm_mhz"] or f_max / 1e6) * 1e6),
@@ -745,7 +749,10 @@ def run_clahe(args, rk):
                 "ms_per_step": e2e_s * 1e3, "what": "api.adaptive_histogram_equalization: host frames in, host frames out"},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": "clahe_lut_kernel + clahe_apply_kernel", "achieved": alg / (ms_step * 1e-3) / 1e9, "peak": hbm,
-                     "unit": "GB/s", "frac": alg / (ms_step * 1e-3) / 1e9 / hbm, "traffic": None, "algorithmic_bytes_per_launch": alg,
+                     "unit": "GB/s", "frac": alg / (ms_step * 1e-3) / 1e9 / hbm, "algorithmic_bytes_per_launch": alg,
+                     # ncu --set full of the three kernels of one 64 x 1080p pass (profiles/r02_clahe_ncu_summary.txt): 132.73 + 3.90,
+                     # 1.05, 143.39 + 73.83 MB -- below the algorithmic 3 B/px because part of the apply pass's re-read hits L2
+                     "traffic": 354898432 if (H, W, N) == (1080, 1920, 64) else None,
                      "peak_is": f"copy bandwidth, {peak_src}"},
         "cpu_baseline": cpu,
     }
